@@ -1,0 +1,151 @@
+"""ctypes loaders for the two CHECKERS.  Test infrastructure: import only from tests/, bench.py's cpu_baseline /
+--impl reference legs and __graft_entry__.smoke() -- never from the product package.
+
+  ref()  -> oracle/_ref/libref_oracle.so   the unmodified reference sources + oracle/ref_harness.cpp
+  port() -> oracle/_build/librt_oracle.so  the plain-C restatement oracle/rt_oracle.c
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SO = os.path.join(HERE, "_ref", "libref_oracle.so")
+PORT_SO = os.path.join(HERE, "_build", "librt_oracle.so")
+_cache = {}
+
+
+def build(which: str = "all") -> None:
+    subprocess.run(["make", "-C", HERE, "-j8", which], check=True, stdout=subprocess.DEVNULL)
+
+
+def ref_available() -> bool:
+    return os.path.exists(REF_SO)
+
+
+def ref():
+    if "ref" not in _cache:
+        if not os.path.exists(REF_SO):
+            raise FileNotFoundError(f"{REF_SO}: build it with `make -C oracle ref` where /root/reference exists")
+        _cache["ref"] = C.CDLL(REF_SO)
+    return _cache["ref"]
+
+
+def port():
+    if "port" not in _cache:
+        if not os.path.exists(PORT_SO):
+            build("port")
+        _cache["port"] = C.CDLL(PORT_SO)
+    return _cache["port"]
+
+
+class Checker:
+    """Uniform Python face of either checker library (entry points ref_* / ora_* have identical signatures)."""
+
+    def __init__(self, kind: str):
+        from radiative_transfer_b200 import abi
+        self.abi = abi
+        self.kind = kind
+        self.lib = ref() if kind == "ref" else port()
+        self.pfx = "ref_" if kind == "ref" else "ora_"
+
+    def _f(self, name):
+        return getattr(self.lib, self.pfx + name)
+
+    def _views(self, p):
+        d, h1 = p.desc()
+        s, h2 = p.layer_soa()
+        return d, s, (h1, h2)
+
+    def lu_solve(self, a, b):
+        a = np.array(a, dtype=np.float64, order="C"); b = np.array(b, dtype=np.float64)
+        self._f("lu_solve")(self.abi.dptr(a), self.abi.dptr(b), C.c_int(b.shape[0]))
+        return b
+
+    def esc_func(self, p, gamma, delta):
+        d, s, hold = self._views(p)
+        gamma = np.ascontiguousarray(gamma, dtype=np.float64); delta = np.ascontiguousarray(delta, dtype=np.float64)
+        out = np.empty_like(gamma)
+        rc = self._f("esc_func")(C.byref(d), gamma.shape[0], self.abi.dptr(gamma), self.abi.dptr(delta), self.abi.dptr(out))
+        assert rc == 0
+        return out
+
+    def overlap_esc_func(self, p, which, gamma, delta, gratio, dx):
+        d, s, hold = self._views(p)
+        arrs = [np.ascontiguousarray(x, dtype=np.float64) for x in (gamma, delta, gratio, dx)]
+        out = np.empty_like(arrs[0])
+        rc = self._f("overlap_esc_func")(C.byref(d), which, arrs[0].shape[0], *[self.abi.dptr(x) for x in arrs], self.abi.dptr(out))
+        assert rc == 0
+        return out
+
+    def dust_absorption(self, p, lay, energy):
+        d, s, hold = self._views(p)
+        energy = np.ascontiguousarray(energy, dtype=np.float64); out = np.empty_like(energy)
+        rc = self._f("dust_absorption")(C.byref(d), C.byref(s), lay, energy.shape[0], self.abi.dptr(energy), self.abi.dptr(out))
+        assert rc == 0, "dust wavelength round trip not exact" if rc == 2 else rc
+        return out
+
+    def line_groups(self, p):
+        d, s, hold = self._views(p)
+        g = np.zeros((4 * p.N * p.N // 4 + 8, 5), dtype=np.int32); n = C.c_int()
+        rc = self._f("line_groups")(C.byref(d), g.shape[0], self.abi.iptr(g), C.byref(n))
+        assert rc == 0
+        return g[: n.value].copy()
+
+    def collision_rates(self, p):
+        d, s, hold = self._views(p)
+        out = np.zeros((p.L, p.N, p.N))
+        assert self._f("collision_rates")(C.byref(d), C.byref(s), self.abi.dptr(out)) == 0
+        return out
+
+    def assemble(self, p, pop):
+        d, s, hold = self._views(p)
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        M = np.zeros((p.L, p.N, p.N)); df = np.zeros((p.L, p.N))
+        assert self._f("assemble")(C.byref(d), C.byref(s), self.abi.dptr(pop), self.abi.dptr(M), self.abi.dptr(df)) == 0
+        return M, df
+
+    def step(self, p, pop):
+        d, s, hold = self._views(p)
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        new = np.zeros((p.L, p.N)); eq = np.zeros(p.L)
+        assert self._f("step")(C.byref(d), C.byref(s), self.abi.dptr(pop), self.abi.dptr(new), self.abi.dptr(eq)) == 0
+        return new, eq
+
+    def intensity(self, p, lay, up, low, pop):
+        d, s, hold = self._views(p)
+        up = np.ascontiguousarray(up, dtype=np.int32); low = np.ascontiguousarray(low, dtype=np.int32)
+        pop = np.ascontiguousarray(pop, dtype=np.float64); out = np.zeros(up.shape[0])
+        assert self._f("intensity")(C.byref(d), C.byref(s), lay, up.shape[0], self.abi.iptr(up), self.abi.iptr(low),
+                                    self.abi.dptr(pop), self.abi.dptr(out)) == 0
+        return out
+
+    def boundary(self, p):
+        d, s, hold = self._views(p)
+        pop = np.zeros((p.L, p.N))
+        assert self._f("boundary")(C.byref(d), C.byref(s), self.abi.dptr(pop)) == 0
+        return pop
+
+    def boltzmann(self, p):
+        d, s, hold = self._views(p)
+        pop = np.zeros((p.L, p.N))
+        assert self._f("boltzmann")(C.byref(d), C.byref(s), self.abi.dptr(pop)) == 0
+        return pop
+
+    def solve(self, p, start_mode=None, max_iter=None, min_err=1e-5, accel=None, retry=False, max_iter_ext=15000,
+              pop0=None, lay=(0, -1), nthreads=1):
+        """Returns (pop [L,N], status recarray [L], seconds)."""
+        d, s, hold = self._views(p)
+        start_mode = p.start_mode if start_mode is None else start_mode
+        max_iter = p.max_iter if max_iter is None else max_iter
+        accel = p.accel if accel is None else accel
+        pop = np.zeros((p.L, p.N)) if pop0 is None else np.array(pop0, dtype=np.float64, order="C")
+        st = np.zeros(p.L, dtype=self.abi.STATUS_DTYPE); sec = C.c_double()
+        rc = self._f("solve")(C.byref(d), C.byref(s), self.abi.dptr(pop), start_mode, max_iter, C.c_double(min_err),
+                              int(accel), int(retry), max_iter_ext, st.ctypes.data_as(C.POINTER(self.abi.rt_layer_status)),
+                              lay[0], lay[1], nthreads, C.byref(sec))
+        assert rc == 0, rc
+        return pop, st, sec.value
