@@ -225,6 +225,7 @@ rt_status rt_set_populations(rt_model* m, const double* pop);
  * the last reset.  names/ms/launches arrays of capacity `cap`; returns number of classes through *n. */
 rt_status rt_profile_reset(rt_model* m, int enable_timing);
 rt_status rt_profile_get(rt_model* m, int cap, const char** names, double* ms, long long* launches, int* n);
+long long rt_iterations_enqueued(const rt_model* m); /* controller steps enqueued since rt_profile_reset */
 
 /* Post-solve maser quantities (transition_data.cpp:210-378): for each listed transition (up[i] > low[i]):
  * inv[L], gain[L] per layer and the scalars {inv, gain, tau_eff, tau_max, lay_nb_hg}; tau_vs_aspect [na],

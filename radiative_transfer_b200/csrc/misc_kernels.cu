@@ -1,0 +1,113 @@
+// misc_kernels.cu -- single-line intensity probe (rt_intensity) and the post-solve maser pass (rt_maser_postpass).
+#include "physics.cuh"
+
+// == virtual intensity_calc(up, low, level_pop, J) of the active scheme for one layer (iteration_lvg.cpp:163-185,
+// overlap single-line overload :503-526).  which: 0 = single line, 1 = first line of a pair, 2 = second line.
+__global__ void k_intensity_single(DevModel d, int lay, int u1, int l1, double A1ul, double A1lu, int u2, int l2,
+                                   double A2ul, double A2lu, int which, const double* __restrict__ pop, double* out)
+{
+    const LayerCtx c = dev_layer_ctx(d, lay);
+    double sigma[RT_MAX_DUST];
+    // dust cross-section at the energy of line 1, evaluated here from the per-line table when the line is known,
+    // else passed through out[1..ncomp] by the host
+    for (int k = 0; k < d.ncomp; k++) sigma[k] = out[1 + k];
+    const double e1 = d.energy[u1] - d.energy[l1];
+    if (which == 0) out[0] = dev_intensity_single(d, c, e1, A1ul, A1lu, pop[u1], pop[l1], sigma);
+    else {
+        double J1, J2;
+        const double dxn = (d.energy[u1] - d.energy[l1] - d.energy[u2] + d.energy[l2]) * d.prm.speed_of_light;
+        dev_intensity_pair(d, c, e1, dxn, A1ul, A1lu, A2ul, A2lu, pop[u1], pop[l1], pop[u2], pop[l2], sigma, J1, J2);
+        out[0] = which == 1 ? J1 : J2;
+    }
+}
+
+void launch_intensity_single(const DevModel& d, cudaStream_t s, int lay, int up, int low, double Aul, double Alu,
+                             int pair_up, int pair_low, double pAul, double pAlu, int which, const double* pop_dev,
+                             double* out_dev)
+{
+    k_intensity_single<<<1, 1, 0, s>>>(d, lay, up, low, Aul, Alu, pair_up, pair_low, pAul, pAlu, which, pop_dev, out_dev);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K5: post-solve maser quantities of listed transitions, transition_data.cpp:210-378
+// (calc_inv :210-223, calc_gain :240-294 without the oH2O 22 GHz special width, calc_line_profile :296-378).
+// One CTA per transition.  Layer sums run in ascending layer order like the reference's loops.
+// ------------------------------------------------------------------------------------------------------------
+struct PostArgs {
+    const double* pop;  // [L][N]
+    const int *up, *low;
+    const double* sigma; // [T][ncomp] dust cross-section at the transition energy
+    const double *dz, *vel_n, *vgrid; // [L], [L], [nb_freq]
+    double height, delta_aspect;
+    int nb_freq, nb_aspect;
+    double *inv_arr, *gain_arr, *scalars, *tau_aspect, *tau_freq;
+};
+
+__global__ void __launch_bounds__(320) k_postpass(DevModel d, PostArgs a)
+{
+    const int t = blockIdx.x, L = d.L, N = d.N;
+    extern __shared__ double sm[]; // line_opacity[L], dust_opacity[L], inv[L], gain[L]
+    double* s_lo = sm; double* s_do = sm + L; double* s_inv = sm + 2 * L; double* s_gain = sm + 3 * L;
+    __shared__ unsigned long long s_tmax[64];
+    const int u = a.up[t], l = a.low[t];
+    const double energy = d.energy[u] - d.energy[l]; // transition::energy, spectroscopy.cpp:1224-1238
+    const double energy_th = energy * energy * energy;
+    const double gu = d.g[u], gl = d.g[l];
+    const double Aul = d.einst[(size_t)u * N + l];
+    for (int lay = threadIdx.x; lay < L; lay += blockDim.x) {
+        const double up_pop = a.pop[(size_t)lay * N + u], low_pop = a.pop[(size_t)lay * N + l];
+        const double inv = up_pop / gu - low_pop / gl; // :218
+        const double vel = d.vel_width[lay];           // pow(2kT/m + vt^2, 0.5), :261-262 == iteration_lvg.cpp:65
+        const double line_gain = inv * gu * Aul * d.prm.onedivby_sqrt_pi * d.mol_conc[lay] / (energy_th * d.prm.eight_pi * vel); // :266-268
+        double d_abs = 0.;
+        for (int c = 0; c < d.ncomp; c++) d_abs += a.sigma[(size_t)t * d.ncomp + c] * d.dust_conc[(size_t)lay * d.ncomp + c];
+        s_inv[lay] = inv;
+        s_gain[lay] = line_gain - d_abs;
+        s_lo[lay] = inv * gu * Aul * d.mol_conc[lay] * d.prm.onedivby_sqrt_pi / (energy_th * d.prm.eight_pi * vel); // :335-337
+        s_do[lay] = d_abs;
+        if (a.inv_arr) a.inv_arr[(size_t)t * L + lay] = inv;
+        if (a.gain_arr) a.gain_arr[(size_t)t * L + lay] = line_gain - d_abs;
+    }
+    if (threadIdx.x < 64) s_tmax[threadIdx.x] = 0ull;
+    __syncthreads();
+    if (threadIdx.x == 0 && a.scalars) {
+        double inv = 0., gain = 0., tau_eff = 0., g = 0.;
+        int hg = 0;
+        for (int lay = 0; lay < L; lay++) {
+            inv += s_inv[lay] * a.dz[lay];
+            gain += s_gain[lay] * a.dz[lay];
+            if (s_gain[lay] > 0.) tau_eff += s_gain[lay] * a.dz[lay];
+            if (s_gain[lay] > g) { g = s_gain[lay]; hg = lay; }
+        }
+        if (g < 1.e-99) hg = 0;
+        double* s = a.scalars + 5 * (size_t)t;
+        s[0] = inv / a.height; s[1] = gain / a.height; s[2] = tau_eff; s[4] = hg;
+    }
+    const int n = threadIdx.x;
+    if (n < a.nb_freq) {
+        const double vel = a.vgrid[n];
+        for (int i = 0; i < a.nb_aspect; i++) {
+            const double aspect = 1. + a.delta_aspect * i;
+            double tau = 0.;
+            for (int lay = 0; lay < L; lay++) {
+                const double x = (vel - a.vel_n[lay] / aspect) / d.vel_width[lay];
+                const double profile = exp(-x * x);
+                const double k = s_lo[lay] * profile - s_do[lay];
+                if (k > 0.) tau += k * a.dz[lay] * aspect;
+            }
+            atomicMax(&s_tmax[i], (unsigned long long)__double_as_longlong(tau)); // tau >= 0
+            if (i == 0 && a.tau_freq) a.tau_freq[(size_t)t * a.nb_freq + n] = tau;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < a.nb_aspect) {
+        const double v = __longlong_as_double((long long)s_tmax[threadIdx.x]);
+        if (a.tau_aspect) a.tau_aspect[(size_t)t * a.nb_aspect + threadIdx.x] = v;
+        if (threadIdx.x == 0 && a.scalars) a.scalars[5 * (size_t)t + 3] = v; // tau_max = tau_vs_aspect_ratio[0]
+    }
+}
+
+void launch_postpass_impl(const DevModel& d, cudaStream_t s, const PostArgs& a, int nb_trans)
+{
+    if (nb_trans > 0) k_postpass<<<nb_trans, 320, 4 * d.L * sizeof(double), s>>>(d, a);
+}

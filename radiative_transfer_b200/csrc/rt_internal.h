@@ -1,0 +1,120 @@
+// rt_internal.h -- device-side data layout and kernel launchers of librt_b200.so (not part of the C ABI).
+//
+// HBM layout (everything FP64, layer-major):
+//   Cmat [L][Np][Np]  collisional part of the rate matrix of every layer, in the layout of the reference's
+//                     `matrix` (iteration_lvg.cpp:127-131): entry [j][i] = rate i->j, diagonal = -(column sum).
+//                     Built ONCE per cloud (it depends on the layer only).
+//   Mmat [L][Np][Np]  per-iteration rate matrix = Cmat + radiative terms, row 0 = 1; destroyed by the LU.
+//   Np = N rounded up to a multiple of 32; the padding is an identity block so that every blocked kernel works
+//   on whole 32x32 tiles without edge cases (padded unknowns solve to 0 and never couple to real levels).
+//   pop  [L][N]       current populations (pop_old of iteration_control::next_step)
+//   rhs  [L][Np]      right-hand side e0 -> solution (new populations)
+//   hist_pop/hist_res [L][6][N]  rings of the last nb_prev_steps+1 population / residual vectors
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <string>
+#include <vector>
+#include "../../include/rt_b200.h"
+
+#define RT_HIST 6
+#define RT_MAX_TABLES 16
+#define RT_MAX_DUST 8
+#define RT_NB 32 // LU panel width == padding granularity
+
+struct DevTable {            // one collision_data, transposed to [jmax][imax] so one layer's T-row is contiguous
+    int nb_lev, jmax, imax, pad;
+    double max_temp;
+    const double* tgrid;     // [jmax]
+    const double* coeff_t;   // [jmax][imax]
+    const double* deriv_t;   // [jmax][imax]
+};
+
+struct DevLvg { int nb_d, nb_g; const double *delta, *gamma, *p; };
+struct DevOverlap { int nb_d, nb_dx, nb_gr, nb_g; const double *log_delta, *dx, *gratio, *gamma, *p; };
+
+// Everything a kernel needs, passed by value (fits the 4 KB parameter space).
+struct DevModel {
+    int N, Np, R, G, L, ncomp, K, nb1, nb2, rule, scheme, pad0;
+    rt_params prm;
+    double mol_mass;
+    // levels
+    const double* energy; const int* g; const int* v; const double* jq;
+    const double* einst;     // [N][N] dense, only read by the boundary-start variant of K0
+    // radiative transitions (lines): u > l
+    const int *tr_u, *tr_l;
+    const double *tr_Aul, *tr_Alu, *tr_E, *tr_sigma; // tr_sigma [R][ncomp] dust cross-section at the line energy
+    // groups of 1 or 2 lines whose J is evaluated together: {nb, lineA, lineB}; LVG scheme: G == R, nb == 1
+    const int* grp;          // [G][3]
+    const double* grp_dxn;   // [G] (E_u1 - E_l1 - E_u2 + E_l2) * c: numerator of dx (iteration_lvg.cpp:455); 0 for singles
+    // per-row sparse list of radiative entries: row i holds (col, line, kind) kind 0: i == upper, 1: i == lower
+    const int *row_ptr, *row_col, *row_line;
+    DevTable tab[RT_MAX_TABLES];
+    DevLvg lvg;
+    DevOverlap ov[2];
+    // layers (SoA, [L])
+    const double *temp_n, *temp_el, *mol_conc, *vel_width, *vel_grad, *dust_conc /*[L][ncomp]*/;
+    const double* conc;      // [L][K] partner concentrations (set_gas_param)
+    const int* tidx;         // [L][K] temperature indices (collision_data::locate)
+    // big per-layer state
+    double *Cmat, *Mmat, *pop, *rhs, *hist_pop, *hist_res, *opt, *yd, *yu;
+    int* ipiv;               // [L][Np]
+    // controller state [L]
+    int *iter_nb, *nb_after, *head_pop, *head_res, *n_hist_pop, *n_hist_res, *conv, *active_flag;
+    double *best_eq, *eq_err, *pop_err, *rel_err;
+    unsigned long long* eq_bits; // [L] max |df| of the current assembly as ordered bits
+    int *active, *n_active;  // compacted list of layers still iterating
+};
+
+struct rt_model {
+    int device = 0;
+    DevModel d{};
+    rt_model_desc desc{};          // shallow copy of scalars only
+    std::string mol_name;
+    std::string last_error;
+    std::vector<void*> allocs;     // every cudaMalloc, freed in rt_model_destroy
+    std::vector<void*> cloud_allocs;
+    cudaStream_t stream = nullptr;
+    int* h_n_active = nullptr;     // pinned
+    bool has_cloud = false;
+    // host copies needed by host-side entry points
+    std::vector<double> h_energy, h_einst;
+    std::vector<int> h_tr_u, h_tr_l, h_grp;
+    std::vector<rt_layer_status> h_status;
+    std::vector<double> h_dz, h_vel_n, h_vel_turb;
+    double h_height = 0.;
+    long long iters_enqueued = 0;
+    std::vector<std::vector<double>> h_dust_en, h_dust_abs;
+    std::vector<double> h_dust_exp;
+    // profiling
+    bool prof_timing = false;
+    std::vector<std::string> prof_names;
+    std::vector<double> prof_ms;
+    std::vector<long long> prof_launches;
+    std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_pending;
+    std::vector<cudaEvent_t> ev_pool;
+};
+
+// ---- kernel launchers (each returns after enqueueing on `s`) -------------------------------------------------
+// layers processed = active[0 .. min(*n_active, nlay_bound))
+void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int neutrals_only_half_A);
+void launch_intensity(const DevModel& d, cudaStream_t s, int nlay_bound);
+void launch_assemble(const DevModel& d, cudaStream_t s, int nlay_bound, double* df_out /*[L][N] or null*/);
+void launch_lu_solve(rt_model* m, cudaStream_t s, int nlay_bound);
+void launch_ctl_init_flagged(const DevModel& d, cudaStream_t s, int accel);
+void launch_ctl_step(const DevModel& d, cudaStream_t s, int nlay_bound, int accel, int max_iter, double min_err);
+void launch_compact(const DevModel& d, cudaStream_t s);
+void launch_set_active_range(const DevModel& d, cudaStream_t s, int lay_begin, int lay_end);
+void launch_set_active_failed(const DevModel& d, cudaStream_t s, int lay_begin, int lay_end);
+void launch_boltzmann(const DevModel& d, cudaStream_t s);
+void launch_set_rhs(const DevModel& d, cudaStream_t s, int nlay_bound);
+void launch_set_row0(const DevModel& d, cudaStream_t s, int nlay_bound);
+void launch_copy_rhs_to_pop(const DevModel& d, cudaStream_t s, int nlay_bound);
+void launch_intensity_single(const DevModel& d, cudaStream_t s, int lay, int up, int low, double Aul, double Alu,
+                             int pair_up, int pair_low, double pAul, double pAlu, int which, const double* pop_dev,
+                             double* out_dev);
+
+// profiling hooks used by the launchers
+int rt_prof_class(rt_model* m, const char* name);
+void rt_prof_begin(rt_model* m, int cls, cudaStream_t s);
+void rt_prof_end(rt_model* m, int cls, cudaStream_t s);

@@ -1,0 +1,196 @@
+"""Host-side mirror of the reference's solver entry points over the C ABI (include/rt_b200.h).
+
+`Model` plays the role of the objects the reference driver builds around one molecule
+(`iteration_scheme_lvg` + `iteration_control`, radiative_transfer.cpp:664-670): create it from a `Problem`,
+upload a cloud, call `calc_molecular_populations` / `calculate_populations` / `calc_new_pop` / `intensity_calc`.
+Everything is computed by librt_b200.so on the GPU; there is no CPU path and a missing library is an error.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from . import abi
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librt_b200.so")
+_lib = None
+
+ENTRY_POINTS = [
+    "rt_params_default", "rt_status_string", "rt_last_error", "rt_abi_version", "rt_model_create", "rt_model_destroy",
+    "rt_cloud_upload", "rt_boundary_populations", "rt_step", "rt_assemble", "rt_intensity", "rt_solve",
+    "rt_calc_molecular_populations", "rt_solve_device", "rt_get_status", "rt_get_populations", "rt_set_populations",
+    "rt_profile_reset", "rt_profile_get", "rt_iterations_enqueued", "rt_maser_postpass",
+]
+
+
+class RtError(RuntimeError):
+    pass
+
+
+def build_library() -> None:
+    """nvcc -gencode arch=compute_100a,code=sm_100a ... (radiative_transfer_b200/csrc/Makefile); works without a GPU."""
+    subprocess.run(["make", "-C", os.path.join(HERE, "csrc"), "-j8"], check=True, stdout=subprocess.DEVNULL)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RtError(f"{LIB_PATH} is missing: build it with __graft_entry__.build() (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.rt_status_string.restype = C.c_char_p
+        L.rt_last_error.restype = C.c_char_p
+        L.rt_last_error.argtypes = [C.c_void_p]
+        L.rt_iterations_enqueued.restype = C.c_longlong
+        L.rt_iterations_enqueued.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+class Model:
+    def __init__(self, problem: abi.Problem, device: int = 0, upload_cloud: bool = True):
+        self.p = problem
+        self.L_ = lib()
+        self.h = C.c_void_p()
+        d, hold = problem.desc()
+        rc = self.L_.rt_model_create(C.byref(d), int(device), C.byref(self.h))
+        if rc != abi.RT_OK:
+            raise RtError(f"rt_model_create: {self.L_.rt_status_string(rc).decode()}: {self.L_.rt_last_error(None).decode()}")
+        self.N = problem.N
+        self.L = 0
+        if upload_cloud:
+            self.cloud_upload(problem)
+
+    # -- helpers -------------------------------------------------------------------------------------------
+    def _ck(self, rc, what):
+        if rc != abi.RT_OK:
+            raise RtError(f"{what}: {self.L_.rt_status_string(rc).decode()}: {self.L_.rt_last_error(self.h).decode()}")
+
+    def close(self):
+        if self.h:
+            self.L_.rt_model_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _st(self):
+        return np.zeros(self.L, dtype=abi.STATUS_DTYPE)
+
+    @staticmethod
+    def _stp(st):
+        return st.ctypes.data_as(C.POINTER(abi.rt_layer_status))
+
+    # -- the reference's per-layer setters, for all layers at once (radiative_transfer.cpp:238-242) ----------
+    def cloud_upload(self, problem: abi.Problem):
+        s, hold = problem.layer_soa()
+        self._ck(self.L_.rt_cloud_upload(self.h, C.byref(s)), "rt_cloud_upload")
+        self.L = problem.L
+
+    # -- boundary_layer_populations (iteration_control.cpp:52-91) ---------------------------------------------
+    def boundary_layer_populations(self):
+        pop = np.zeros((self.L, self.N))
+        self._ck(self.L_.rt_boundary_populations(self.h, abi.dptr(pop)), "rt_boundary_populations")
+        return pop
+
+    # -- iteration_scheme_lvg::operator() (iteration_lvg.cpp:112-161) -----------------------------------------
+    def assemble(self, pop):
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        M = np.zeros((self.L, self.N, self.N)); df = np.zeros((self.L, self.N))
+        self._ck(self.L_.rt_assemble(self.h, abi.dptr(pop), abi.dptr(M), abi.dptr(df)), "rt_assemble")
+        return M, df
+
+    # -- iteration_scheme_lvg::calc_new_pop (iteration_lvg.cpp:87-110) ----------------------------------------
+    def calc_new_pop(self, old_pop):
+        old_pop = np.ascontiguousarray(old_pop, dtype=np.float64)
+        new = np.zeros((self.L, self.N)); eq = np.zeros(self.L)
+        self._ck(self.L_.rt_step(self.h, abi.dptr(old_pop), abi.dptr(new), abi.dptr(eq)), "rt_step")
+        return new, eq
+
+    # -- intensity_calc (iteration_lvg.cpp:163-185 / :503-526) ------------------------------------------------
+    def intensity_calc(self, lay, up, low, pop):
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        out = C.c_double()
+        self._ck(self.L_.rt_intensity(self.h, int(lay), int(up), int(low), abi.dptr(pop), C.byref(out)), "rt_intensity")
+        return out.value
+
+    # -- iteration_control::calculate_populations (iteration_control.h:196-242), every layer ------------------
+    def calculate_populations(self, pop0=None, start_mode=None, max_iter=None, min_err=1e-5, accel=None):
+        p = self.p
+        start_mode = p.start_mode if start_mode is None else start_mode
+        if pop0 is not None:
+            start_mode = abi.RT_START_GIVEN
+        pop = np.zeros((self.L, self.N)) if pop0 is None else np.array(pop0, dtype=np.float64, order="C")
+        st = self._st()
+        self._ck(self.L_.rt_solve(self.h, abi.dptr(pop), int(start_mode), int(p.max_iter if max_iter is None else max_iter),
+                                  C.c_double(min_err), int(p.accel if accel is None else accel), self._stp(st)), "rt_solve")
+        return pop, st
+
+    # -- calc_molecular_populations (radiative_transfer.cpp:219-289) incl. retry policy -----------------------
+    def calc_molecular_populations(self, acceleration=None, start_mode=None, pop0=None, max_iter_acc=150,
+                                   max_iter_ext=15000, min_err=1e-5):
+        p = self.p
+        start_mode = p.start_mode if start_mode is None else start_mode
+        if pop0 is not None:
+            start_mode = abi.RT_START_GIVEN
+        pop = np.zeros((self.L, self.N)) if pop0 is None else np.array(pop0, dtype=np.float64, order="C")
+        st = self._st()
+        self._ck(self.L_.rt_calc_molecular_populations(self.h, abi.dptr(pop), int(start_mode),
+                                                       int(p.accel if acceleration is None else acceleration),
+                                                       int(max_iter_acc), int(max_iter_ext), C.c_double(min_err),
+                                                       self._stp(st)), "rt_calc_molecular_populations")
+        return pop, st
+
+    # -- device-resident variant (bench `value`) ---------------------------------------------------------------
+    def solve_device(self, start_mode=None, max_iter=None, min_err=1e-5, accel=None):
+        p = self.p
+        self._ck(self.L_.rt_solve_device(self.h, int(p.start_mode if start_mode is None else start_mode),
+                                         int(p.max_iter if max_iter is None else max_iter), C.c_double(min_err),
+                                         int(p.accel if accel is None else accel)), "rt_solve_device")
+
+    def get_status(self):
+        st = self._st()
+        self._ck(self.L_.rt_get_status(self.h, self._stp(st)), "rt_get_status")
+        return st
+
+    def get_populations(self):
+        pop = np.zeros((self.L, self.N))
+        self._ck(self.L_.rt_get_populations(self.h, abi.dptr(pop)), "rt_get_populations")
+        return pop
+
+    def set_populations(self, pop):
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        self._ck(self.L_.rt_set_populations(self.h, abi.dptr(pop)), "rt_set_populations")
+
+    # -- transition_data_container::calc_inv / calc_gain / calc_line_profile ------------------------------------
+    def maser_postpass(self, pop, up, low, nb_freq=300, nb_aspect=37, delta_aspect=0.25, velocity_shift=5.e5):
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        up = np.ascontiguousarray(up, dtype=np.int32); low = np.ascontiguousarray(low, dtype=np.int32)
+        T = up.shape[0]
+        out = dict(inv=np.zeros((T, self.L)), gain=np.zeros((T, self.L)), scalars=np.zeros((T, 5)),
+                   tau_vs_aspect=np.zeros((T, nb_aspect)), tau_vs_freq=np.zeros((T, nb_freq)))
+        self._ck(self.L_.rt_maser_postpass(self.h, abi.dptr(pop), T, abi.iptr(up), abi.iptr(low), nb_freq, nb_aspect,
+                                           C.c_double(delta_aspect), C.c_double(velocity_shift), abi.dptr(out["inv"]),
+                                           abi.dptr(out["gain"]), abi.dptr(out["scalars"]), abi.dptr(out["tau_vs_aspect"]),
+                                           abi.dptr(out["tau_vs_freq"])), "rt_maser_postpass")
+        return out
+
+    # -- instrumentation --------------------------------------------------------------------------------------
+    def profile_reset(self, timing: bool = False):
+        self._ck(self.L_.rt_profile_reset(self.h, int(timing)), "rt_profile_reset")
+
+    def profile_get(self):
+        cap = 64
+        names = (C.c_char_p * cap)(); ms = (C.c_double * cap)(); ln = (C.c_longlong * cap)(); n = C.c_int()
+        self._ck(self.L_.rt_profile_get(self.h, cap, names, ms, ln, C.byref(n)), "rt_profile_get")
+        return {names[i].decode(): (ms[i], ln[i]) for i in range(n.value)}
+
+    def iterations_enqueued(self) -> int:
+        return int(self.L_.rt_iterations_enqueued(self.h))
