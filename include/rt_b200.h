@@ -188,6 +188,11 @@ rt_status rt_model_destroy(rt_model* m);
  * the per-layer collisional matrix C(layer) on device (set_gas_param + get_rate_neutrals/electrons). */
 rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* layers);
 
+/* Re-runs the collisional-matrix kernel from the layer arrays already resident in HBM (what rt_cloud_upload does
+ * after its host-to-device copies); bench.py's device-resident `value` leg calls it so that every timed step
+ * contains the whole per-cloud work. */
+rt_status rt_cloud_rebuild(rt_model* m);
+
 /* == boundary_layer_populations for every layer (iteration_control.cpp:52-91); pop is HOST [L*N]. */
 rt_status rt_boundary_populations(rt_model* m, double* pop);
 
@@ -226,6 +231,17 @@ rt_status rt_set_populations(rt_model* m, const double* pop);
 rt_status rt_profile_reset(rt_model* m, int enable_timing);
 rt_status rt_profile_get(rt_model* m, int cap, const char** names, double* ms, long long* launches, int* n);
 long long rt_iterations_enqueued(const rt_model* m); /* controller steps enqueued since rt_profile_reset */
+long long rt_launch_count(void); /* kernels launched by this library in this process so far (bench.py gpu_launches) */
+/* ALGORITHMIC flops / bytes of the launches of each class since the last reset (same order as rt_profile_get):
+ * per-layer figure of DESIGN.md x the layers each launch processed. */
+rt_status rt_profile_get_work(rt_model* m, int cap, double* flops, double* bytes);
+/* CUDA-event stopwatch on the library's own stream (torch.cuda.Event only sees torch's stream). */
+rt_status rt_timer_begin(rt_model* m);
+rt_status rt_timer_end(rt_model* m, double* ms);
+/* Measured FP64 ceilings of `device`: a register-resident DFMA loop and a DMMA (mma.sync.m8n8k4.f64) loop on every
+ * SM, TFLOP/s, best of `reps`.  MEASURED_PEAKS.json holds no FP64 figure, so bench.py measures the denominator of
+ * the LU roofline in the same run. */
+rt_status rt_device_fp64_peak(int device, int reps, double* dfma_tflops, double* dmma_tflops);
 
 /* Post-solve maser quantities (transition_data.cpp:210-378): for each listed transition (up[i] > low[i]):
  * inv[L], gain[L] per layer and the scalars {inv, gain, tau_eff, tau_max, lay_nb_hg}; tau_vs_aspect [na],

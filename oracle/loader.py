@@ -149,3 +149,39 @@ class Checker:
                               lay[0], lay[1], nthreads, C.byref(sec))
         assert rc == 0, rc
         return pop, st, sec.value
+
+    def maser_postpass(self, p, pop, up, low, nb_freq=300, nb_aspect=37, delta_aspect=0.25, velocity_shift=5.e5):
+        """transition_data_container::calc_inv / calc_gain / calc_line_profile.  The reference fixes
+        nb_freq=300, nb_aspect=37, delta_aspect=0.25, velocity_shift=5e5 (transition_data.cpp:16-18,191)."""
+        d, s, hold = self._views(p)
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        up = np.ascontiguousarray(up, dtype=np.int32); low = np.ascontiguousarray(low, dtype=np.int32)
+        T = up.shape[0]
+        out = dict(inv=np.zeros((T, p.L)), gain=np.zeros((T, p.L)), scalars=np.zeros((T, 5)),
+                   tau_vs_aspect=np.zeros((T, nb_aspect)), tau_vs_freq=np.zeros((T, nb_freq)))
+        tail = [self.abi.dptr(out[k]) for k in ("inv", "gain", "scalars", "tau_vs_aspect", "tau_vs_freq")]
+        if self.kind == "ref":
+            assert (nb_freq, nb_aspect, delta_aspect, velocity_shift) == (300, 37, 0.25, 5.e5)
+            rc = self.lib.ref_maser_postpass(C.byref(d), C.byref(s), self.abi.dptr(pop), T, self.abi.iptr(up),
+                                             self.abi.iptr(low), *tail)
+        else:
+            rc = self.lib.ora_maser_postpass(C.byref(d), C.byref(s), self.abi.dptr(pop), T, self.abi.iptr(up),
+                                             self.abi.iptr(low), nb_freq, nb_aspect, C.c_double(delta_aspect),
+                                             C.c_double(velocity_shift), *tail)
+        assert rc == 0
+        return out
+
+    def calc_molecular_populations(self, p, acceleration=None):
+        """The warm-start chain + retry policy of calc_molecular_populations (radiative_transfer.cpp:219-289).
+        ref: the reference function itself; port: ora_solve with RT_START_CHAINED."""
+        accel = p.accel if acceleration is None else acceleration
+        if self.kind != "ref":
+            return self.solve(p, start_mode=self.abi.RT_START_CHAINED, accel=accel, retry=True,
+                              max_iter=150 if accel else 15000)
+        d, s, hold = self._views(p)
+        pop = np.zeros((p.L, p.N))
+        st = np.zeros(p.L, dtype=self.abi.STATUS_DTYPE); sec = C.c_double()
+        rc = self.lib.ref_calc_molecular_populations(C.byref(d), C.byref(s), self.abi.dptr(pop), int(accel),
+                                                     st.ctypes.data_as(C.POINTER(self.abi.rt_layer_status)), C.byref(sec))
+        assert rc == 0
+        return pop, st, sec.value

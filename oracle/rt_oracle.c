@@ -965,3 +965,87 @@ int ora_solve(const rt_model_desc* d, const rt_layer_soa* lay, double* pop, int 
     model_destroy(m);
     return 0;
 }
+
+/* transition_data_container::calc_inv (transition_data.cpp:210-223), calc_gain (:240-294, general line-width
+ * branch: the oH2O 6_16-5_23 special width needs the k1/k2 quantum numbers, which the flat model does not carry)
+ * and calc_line_profile (:296-378) for listed transitions.  scalars [nb_trans][5] = {inv, gain, tau_eff, tau_max,
+ * lay_nb_hg}.  nb_freq / nb_aspect / delta_aspect / velocity_shift: 300 / 37 / 0.25 / 5e5 in the reference
+ * (transition_data.cpp:16-18,191). */
+int ora_maser_postpass(const rt_model_desc* d, const rt_layer_soa* lay, const double* pop, int nb_trans, const int* up,
+                       const int* low, int nb_freq, int nb_aspect, double delta_aspect, double velocity_shift,
+                       double* inv_arr, double* gain_arr, double* scalars, double* tau_vs_aspect, double* tau_vs_freq)
+{
+    ora_model* m = model_create(d);
+    const int N = m->N, L = lay->nb_lay;
+    const rt_params* pr = &d->params;
+    double* inv_l = (double*)malloc(sizeof(double) * L);
+    double* gain_l = (double*)malloc(sizeof(double) * L);
+    double* line_opacity = (double*)malloc(sizeof(double) * L);
+    double* dust_opacity = (double*)malloc(sizeof(double) * L);
+    double* vel_width = (double*)malloc(sizeof(double) * L);
+    double* depth = (double*)malloc(sizeof(double) * (size_t)nb_freq * nb_aspect);
+    for (int t = 0; t < nb_trans; t++) {
+        const int u = up[t], l = low[t];
+        const double gu = d->g[u], gl = d->g[l];
+        const double A = d->einst[(size_t)u * N + l];
+        const double energy = d->energy[u] - d->energy[l]; /* transition::energy, spectroscopy.cpp:1224-1238 */
+        const double energy_th = energy * energy * energy;
+        double inv = 0., gain = 0., tau_eff = 0., g = 0.;
+        int hg = 0;
+        for (int k = 0; k < L; k++) { /* calc_inv */
+            inv_l[k] = pop[(size_t)k * N + u] / gu - pop[(size_t)k * N + l] / gl;
+            inv += inv_l[k] * lay->dz[k];
+        }
+        inv /= lay->height;
+        for (int k = 0; k < L; k++) { /* calc_gain :248-272 */
+            const double vel = pow(2. * pr->boltzmann_constant * lay->temp_n[k] / d->mol_mass + lay->vel_turb[k] * lay->vel_turb[k], 0.5);
+            const double line_gain = inv_l[k] * gu * A * pr->onedivby_sqrt_pi * lay->mol_conc[k] / (energy_th * pr->eight_pi * vel);
+            const double d_abs = dust_absorption(m, energy, lay->dust_conc + (size_t)k * lay->dust_ncomp);
+            gain_l[k] = line_gain - d_abs;
+        }
+        for (int k = 0; k < L; k++) { /* :274-289 */
+            gain += gain_l[k] * lay->dz[k];
+            if (gain_l[k] > 0.) tau_eff += gain_l[k] * lay->dz[k];
+            if (gain_l[k] > g) { g = gain_l[k]; hg = k; }
+        }
+        gain /= lay->height;
+        if (g < 1.e-99) hg = 0;
+        /* calc_line_profile */
+        const double vmax = lay->vel_n[0] + velocity_shift, vmin = lay->vel_n[L - 1] - velocity_shift;
+        const double dv = (vmax - vmin) / (nb_freq - 1.);
+        for (int k = 0; k < L; k++) {
+            vel_width[k] = pow(2. * pr->boltzmann_constant * lay->temp_n[k] / d->mol_mass + lay->vel_turb[k] * lay->vel_turb[k], 0.5);
+            line_opacity[k] = inv_l[k] * gu * A * lay->mol_conc[k] * pr->onedivby_sqrt_pi / (energy_th * pr->eight_pi * vel_width[k]);
+            dust_opacity[k] = dust_absorption(m, energy, lay->dust_conc + (size_t)k * lay->dust_ncomp);
+        }
+        for (int i = 0; i < nb_aspect; i++) {
+            const double aspect = 1. + delta_aspect * i;
+            double vel = vmin;
+            for (int n = 0; n < nb_freq; vel += dv, n++) {
+                double tau = 0.;
+                for (int k = 0; k < L; k++) {
+                    const double x = (vel - lay->vel_n[k] / aspect) / vel_width[k];
+                    const double profile = exp(-x * x);
+                    if (line_opacity[k] * profile - dust_opacity[k] > 0.)
+                        tau += (line_opacity[k] * profile - dust_opacity[k]) * lay->dz[k] * aspect;
+                }
+                depth[(size_t)n * nb_aspect + i] = tau;
+            }
+        }
+        for (int i = 0; i < nb_aspect; i++) {
+            double x = 0.;
+            for (int n = 0; n < nb_freq; n++)
+                if (x < depth[(size_t)n * nb_aspect + i]) x = depth[(size_t)n * nb_aspect + i];
+            if (tau_vs_aspect) tau_vs_aspect[(size_t)t * nb_aspect + i] = x;
+            if (i == 0 && scalars) scalars[5 * (size_t)t + 3] = x;
+        }
+        if (tau_vs_freq)
+            for (int n = 0; n < nb_freq; n++) tau_vs_freq[(size_t)t * nb_freq + n] = depth[(size_t)n * nb_aspect];
+        if (inv_arr) memcpy(inv_arr + (size_t)t * L, inv_l, sizeof(double) * L);
+        if (gain_arr) memcpy(gain_arr + (size_t)t * L, gain_l, sizeof(double) * L);
+        if (scalars) { double* s = scalars + 5 * (size_t)t; s[0] = inv; s[1] = gain; s[2] = tau_eff; s[4] = hg; }
+    }
+    free(inv_l); free(gain_l); free(line_opacity); free(dust_opacity); free(vel_width); free(depth);
+    model_destroy(m);
+    return 0;
+}

@@ -309,24 +309,28 @@ __global__ void k_copy_rhs_to_pop(DevModel d, int nlay_bound)
     if (i < d.N) d.pop[(size_t)lay * d.N + i] = d.rhs[(size_t)lay * d.Np + i];
 }
 
-void launch_ctl_init_flagged(const DevModel& d, cudaStream_t s, int accel) { k_ctl_init<<<d.L, CTL_THREADS, 0, s>>>(d, accel); }
+void launch_ctl_init_flagged(const DevModel& d, cudaStream_t s, int accel) { g_rt_launches++; k_ctl_init<<<d.L, CTL_THREADS, 0, s>>>(d, accel); }
 void launch_ctl_step(const DevModel& d, cudaStream_t s, int nlay_bound, int accel, int max_iter, double min_err)
 {
+    g_rt_launches++;
     k_ctl_step<<<nlay_bound, CTL_THREADS, 0, s>>>(d, nlay_bound, accel, max_iter, min_err);
 }
-void launch_compact(const DevModel& d, cudaStream_t s) { k_compact<<<1, 1024, 0, s>>>(d); }
-void launch_set_active_range(const DevModel& d, cudaStream_t s, int b, int e) { k_set_active_range<<<(d.L + 255) / 256, 256, 0, s>>>(d, b, e); }
-void launch_set_active_failed(const DevModel& d, cudaStream_t s, int b, int e) { k_set_active_failed<<<(d.L + 255) / 256, 256, 0, s>>>(d, b, e); }
-void launch_boltzmann(const DevModel& d, cudaStream_t s) { k_boltzmann<<<d.L, 256, 0, s>>>(d); }
+void launch_compact(const DevModel& d, cudaStream_t s) { g_rt_launches++; k_compact<<<1, 1024, 0, s>>>(d); }
+void launch_set_active_range(const DevModel& d, cudaStream_t s, int b, int e) { g_rt_launches++; k_set_active_range<<<(d.L + 255) / 256, 256, 0, s>>>(d, b, e); }
+void launch_set_active_failed(const DevModel& d, cudaStream_t s, int b, int e) { g_rt_launches++; k_set_active_failed<<<(d.L + 255) / 256, 256, 0, s>>>(d, b, e); }
+void launch_boltzmann(const DevModel& d, cudaStream_t s) { g_rt_launches++; k_boltzmann<<<d.L, 256, 0, s>>>(d); }
 void launch_set_rhs(const DevModel& d, cudaStream_t s, int nlay_bound)
 {
+    g_rt_launches++;
     k_set_rhs<<<dim3((d.Np + 255) / 256, nlay_bound), 256, 0, s>>>(d, nlay_bound);
 }
 void launch_set_row0(const DevModel& d, cudaStream_t s, int nlay_bound)
 {
+    g_rt_launches++;
     k_set_row0<<<dim3((d.Np + 255) / 256, nlay_bound), 256, 0, s>>>(d, nlay_bound);
 }
 void launch_copy_rhs_to_pop(const DevModel& d, cudaStream_t s, int nlay_bound)
 {
+    g_rt_launches++;
     k_copy_rhs_to_pop<<<dim3((d.N + 255) / 256, nlay_bound), 256, 0, s>>>(d, nlay_bound);
 }

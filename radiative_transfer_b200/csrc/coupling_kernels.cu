@@ -135,8 +135,10 @@ void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int half
 {
     const int nt = (d.N + 31) / 32;
     dim3 grid(nt, nt, d.L), block(32, 8);
+    g_rt_launches++;
     k_coll_offdiag<<<grid, block, 0, s>>>(d, out, half_A, d.einst);
     dim3 g2((d.Np + 127) / 128, d.L);
+    g_rt_launches++;
     k_coll_diag<<<g2, 128, 0, s>>>(d, out);
 }
 
@@ -182,6 +184,7 @@ void launch_intensity(const DevModel& d, cudaStream_t s, int nlay_bound)
 {
     if (d.G == 0) return;
     dim3 grid((d.G + 127) / 128, nlay_bound);
+    g_rt_launches++;
     k_intensity<<<grid, 128, 0, s>>>(d, nlay_bound);
 }
 
@@ -266,5 +269,6 @@ __global__ void __launch_bounds__(ASM_WARPS * 32) k_assemble(DevModel d, int nla
 void launch_assemble(const DevModel& d, cudaStream_t s, int nlay_bound, double* df_out)
 {
     dim3 grid((d.Np + ASM_WARPS - 1) / ASM_WARPS, nlay_bound);
+    g_rt_launches++;
     k_assemble<<<grid, ASM_WARPS * 32, d.Np * sizeof(double), s>>>(d, nlay_bound, df_out);
 }

@@ -244,22 +244,26 @@ void launch_lu_solve(rt_model* m, cudaStream_t s, int nlay_bound)
     const int c_gemm = rt_prof_class(m, "lu_gemm"), c_back = rt_prof_class(m, "lu_backsolve");
     for (int k = 0; k < nb; k++) {
         const int mrows = Np - k * RT_NB;
+        const int mt = mrows - RT_NB;
         const size_t smem = (size_t)mrows * PNL_LD * sizeof(double);
-        rt_prof_begin(m, c_panel, s);
+        rt_prof_begin(m, c_panel, s, 32. * 32. * mrows, 16. * 32. * mrows);
+        g_rt_launches++;
         k_panel<<<nlay_bound, PNL_THREADS, smem, s>>>(d, k, nlay_bound);
         rt_prof_end(m, c_panel, s);
-        const int mt = mrows - RT_NB;
         if (mt > 0) {
-            rt_prof_begin(m, c_trsm, s);
+            rt_prof_begin(m, c_trsm, s, 32. * 32. * mt, 16. * 32. * mt);
+            g_rt_launches++;
             k_trsm<<<dim3((mt + TRSM_THREADS - 1) / TRSM_THREADS, nlay_bound), TRSM_THREADS, 0, s>>>(d, k, nlay_bound);
             rt_prof_end(m, c_trsm, s);
             const int nt = (mt + GT - 1) / GT;
-            rt_prof_begin(m, c_gemm, s);
+            rt_prof_begin(m, c_gemm, s, 2. * 32. * mt * mt, 16. * (double)mt * mt);
+            g_rt_launches++;
             k_gemm<<<dim3(nt, nt, nlay_bound), 256, 0, s>>>(d, k, nlay_bound);
             rt_prof_end(m, c_gemm, s);
         }
     }
-    rt_prof_begin(m, c_back, s);
+    rt_prof_begin(m, c_back, s, (double)Np * Np, 4. * Np * Np);
+    g_rt_launches++;
     k_backsolve<<<nlay_bound, 256, Np * sizeof(double), s>>>(d, nlay_bound);
     rt_prof_end(m, c_back, s);
 }

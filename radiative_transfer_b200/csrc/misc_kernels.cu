@@ -25,6 +25,7 @@ void launch_intensity_single(const DevModel& d, cudaStream_t s, int lay, int up,
                              int pair_up, int pair_low, double pAul, double pAlu, int which, const double* pop_dev,
                              double* out_dev)
 {
+    g_rt_launches++;
     k_intensity_single<<<1, 1, 0, s>>>(d, lay, up, low, Aul, Alu, pair_up, pair_low, pAul, pAlu, which, pop_dev, out_dev);
 }
 
@@ -109,5 +110,74 @@ __global__ void __launch_bounds__(320) k_postpass(DevModel d, PostArgs a)
 
 void launch_postpass_impl(const DevModel& d, cudaStream_t s, const PostArgs& a, int nb_trans)
 {
-    if (nb_trans > 0) k_postpass<<<nb_trans, 320, 4 * d.L * sizeof(double), s>>>(d, a);
+    if (nb_trans > 0) { g_rt_launches++; k_postpass<<<nb_trans, 320, 4 * d.L * sizeof(double), s>>>(d, a); }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// FP64 ceilings (rt_device_fp64_peak): denominators of the LU roofline, measured in the same run as the bench.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_peak_dfma(double* out, int iters)
+{
+    double a[8], x = 1.0000001 + threadIdx.x * 1e-9, y = 1e-9;
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = i + threadIdx.x;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) a[i] = fma(a[i], x, y);
+    }
+    double s = 0.;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += a[i];
+    if (s == 12345.678) out[0] = s;
+}
+
+__global__ void __launch_bounds__(256) k_peak_dmma(double* out, int iters)
+{
+    double c[8][2];
+#pragma unroll
+    for (int i = 0; i < 8; i++) c[i][0] = c[i][1] = 0.;
+    double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(c[i][0]), "+d"(c[i][1]) : "d"(a), "d"(b));
+    }
+    double s = 0.;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += c[i][0] + c[i][1];
+    if (s == 12345.678) out[0] = s;
+}
+
+extern "C" rt_status rt_device_fp64_peak(int device, int reps, double* dfma_tflops, double* dmma_tflops)
+{
+    if (cudaSetDevice(device) != cudaSuccess) return RT_ERR_CUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return RT_ERR_CUDA;
+    double* out = nullptr;
+    if (cudaMalloc(&out, 64) != cudaSuccess) return RT_ERR_CUDA;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+    double best[2] = {0., 0.};
+    for (int which = 0; which < 2; which++)
+        for (int r = 0; r < reps + 1; r++) {
+            cudaEventRecord(e0);
+            if (which == 0) k_peak_dfma<<<blocks, threads>>>(out, iters);
+            else k_peak_dmma<<<blocks, threads>>>(out, iters);
+            cudaEventRecord(e1);
+            if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(out); return RT_ERR_CUDA; }
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            // DFMA: 8 fma = 16 flop per thread-iteration; DMMA m8n8k4: 2*8*8*4 = 512 flop per warp instruction, 8 per iteration
+            const double flop = which == 0 ? 16. * iters * (double)blocks * threads : 512. * 8. * iters * (double)blocks * (threads / 32);
+            if (r > 0) best[which] = fmax(best[which], flop / (ms * 1e-3) * 1e-12);
+        }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    if (dfma_tflops) *dfma_tflops = best[0];
+    if (dmma_tflops) *dmma_tflops = best[1];
+    return cudaGetLastError() == cudaSuccess ? RT_OK : RT_ERR_CUDA;
 }

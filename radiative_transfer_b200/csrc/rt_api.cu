@@ -25,6 +25,7 @@ void launch_set_active_failed(const DevModel& d, cudaStream_t s, int b, int e);
     } while (0)
 
 static thread_local std::string g_create_error;
+long long g_rt_launches = 0;
 
 template <class T> static T* dev_alloc(rt_model* m, size_t n, bool cloud, bool zero = true)
 {
@@ -329,6 +330,7 @@ extern "C" rt_status rt_model_destroy(rt_model* m)
     free_cloud(m);
     for (void* p : m->allocs) cudaFree(p);
     for (auto& e : m->ev_pool) cudaEventDestroy(e);
+    for (auto& e : m->timer_ev) if (e) cudaEventDestroy(e);
     if (m->h_n_active) cudaFreeHost(m->h_n_active);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
@@ -343,6 +345,8 @@ int rt_prof_class(rt_model* m, const char* name)
     m->prof_names.push_back(name);
     m->prof_ms.push_back(0.);
     m->prof_launches.push_back(0);
+    m->prof_flops.push_back(0.);
+    m->prof_bytes.push_back(0.);
     return (int)m->prof_names.size() - 1;
 }
 static cudaEvent_t get_event(rt_model* m)
@@ -352,28 +356,30 @@ static cudaEvent_t get_event(rt_model* m)
     cudaEventCreate(&e);
     return e;
 }
-void rt_prof_begin(rt_model* m, int cls, cudaStream_t s)
+void rt_prof_begin(rt_model* m, int cls, cudaStream_t s, double flops_per_layer, double bytes_per_layer)
 {
     m->prof_launches[cls]++;
+    m->prof_flops[cls] += flops_per_layer * m->prof_layers;
+    m->prof_bytes[cls] += bytes_per_layer * m->prof_layers;
     if (!m->prof_timing) return;
     cudaEvent_t a = get_event(m), b = get_event(m);
     cudaEventRecord(a, s);
-    m->prof_pending.push_back({cls, {a, b}});
+    m->prof_pending.push_back({cls, a, b});
 }
 void rt_prof_end(rt_model* m, int cls, cudaStream_t s)
 {
     if (!m->prof_timing) return;
-    cudaEventRecord(m->prof_pending.back().second.second, s);
+    cudaEventRecord(m->prof_pending.back().b, s);
 }
 static void prof_collect(rt_model* m)
 {
     for (auto& p : m->prof_pending) {
         float ms = 0.f;
-        cudaEventSynchronize(p.second.second);
-        cudaEventElapsedTime(&ms, p.second.first, p.second.second);
-        m->prof_ms[p.first] += ms;
-        m->ev_pool.push_back(p.second.first);
-        m->ev_pool.push_back(p.second.second);
+        cudaEventSynchronize(p.b);
+        cudaEventElapsedTime(&ms, p.a, p.b);
+        m->prof_ms[p.cls] += ms;
+        m->ev_pool.push_back(p.a);
+        m->ev_pool.push_back(p.b);
     }
     m->prof_pending.clear();
 }
@@ -460,12 +466,27 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
     m->h_status.assign(L, rt_layer_status{});
     // K0: collisional matrix of every layer, once (it does not depend on the populations)
     const int c0 = rt_prof_class(m, "coll_matrix");
-    rt_prof_begin(m, c0, m->stream);
+    m->has_cloud = true;
+    return rt_cloud_rebuild(m);
+}
+
+// K0 from the layer arrays already resident in HBM: collisional matrix of every layer, once per cloud
+// (it does not depend on the populations)
+extern "C" rt_status rt_cloud_rebuild(rt_model* m)
+{
+    if (!m) return RT_ERR_INVALID;
+    if (!m->has_cloud) { m->last_error = "no cloud uploaded"; return RT_ERR_NO_CLOUD; }
+    CK(cudaSetDevice(m->device));
+    const DevModel& d = m->d;
+    const int c0 = rt_prof_class(m, "coll_matrix");
+    m->prof_layers = d.L;
+    double tab_bytes = 0.;
+    for (int k = 0; k < d.K; k++) tab_bytes += 16. * d.tab[k].imax; // coeff + deriv at the layer's temperature index
+    rt_prof_begin(m, c0, m->stream, 0., tab_bytes + 8. * d.N * d.N);
     launch_coll_matrix(d, m->stream, d.Cmat, 0);
     rt_prof_end(m, c0, m->stream);
     CK(cudaStreamSynchronize(m->stream));
     CK(cudaGetLastError());
-    m->has_cloud = true;
     return RT_OK;
 }
 
@@ -476,10 +497,12 @@ static void enqueue_calc_new_pop(rt_model* m, int bound, double* df_out)
     const DevModel& d = m->d;
     cudaStream_t s = m->stream;
     const int c_int = rt_prof_class(m, "intensity"), c_asm = rt_prof_class(m, "assemble");
-    rt_prof_begin(m, c_int, s);
+    // algorithmic bytes per layer: line records {u,l: int32; A_ul,A_lu,E,sigma: f64} + 2 populations in, yd/yu out
+    rt_prof_begin(m, c_int, s, 0., (40. + 16. + 16.) * d.R);
     launch_intensity(d, s, bound);
     rt_prof_end(m, c_int, s);
-    rt_prof_begin(m, c_asm, s);
+    // read C [N][N] + write M [N][N] + pop in + df/rhs out + the sparse radiative list (yd,yu: 16 R; row CSR: 16 R)
+    rt_prof_begin(m, c_asm, s, 2. * d.N * d.N + 4. * d.R, 16. * d.N * d.N + 16. * d.N + 32. * d.R);
     launch_assemble(d, s, bound, df_out);
     rt_prof_end(m, c_asm, s);
     launch_lu_solve(m, s, bound);
@@ -493,7 +516,9 @@ static void enqueue_start(rt_model* m, int start_mode, int bound)
     if (start_mode == RT_START_BOUNDARY) {
         // boundary_layer_populations, iteration_control.cpp:52-91: neutrals + 0.5 A, row 0 = 1, solve
         const int c0 = rt_prof_class(m, "boundary_matrix");
-        rt_prof_begin(m, c0, s);
+        double tab_bytes = 0.;
+        for (int k = 0; k < d.nb1; k++) tab_bytes += 16. * d.tab[k].imax;
+        rt_prof_begin(m, c0, s, 0., tab_bytes + 12. * d.N * d.N);
         launch_coll_matrix(d, s, d.Mmat, 1);
         rt_prof_end(m, c0, s);
         launch_set_row0(d, s, bound);
@@ -516,25 +541,28 @@ static rt_status solve_range(rt_model* m, int lb, int le, int start_mode, int ma
     CK(cudaStreamSynchronize(s));
     int bound = m->h_n_active[0];
     if (bound == 0) return RT_OK;
+    m->prof_layers = bound;
     enqueue_start(m, start_mode, bound);
     launch_ctl_init_flagged(d, s, accel);
     const int c_ctl = rt_prof_class(m, "controller");
+    // n_active after iteration `it` lands in the pinned ring slot (it % RT_RING) + 1; the host reads it one
+    // iteration late, so the GPU always has the next iteration queued while the host looks at the count
     cudaEvent_t ev[2];
     CK(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
     int it = 0;
     for (; it < max_iter && bound > 0; it++) {
         enqueue_calc_new_pop(m, bound, nullptr);
-        rt_prof_begin(m, c_ctl, s);
+        rt_prof_begin(m, c_ctl, s, 0., 8. * 6. * d.N);
         launch_ctl_step(d, s, bound, accel, max_iter, min_err);
         launch_compact(d, s);
         rt_prof_end(m, c_ctl, s);
         CK(cudaMemcpyAsync(m->h_n_active + 1 + (it & 1), d.n_active, sizeof(int), cudaMemcpyDeviceToHost, s));
         CK(cudaEventRecord(ev[it & 1], s));
         if (it >= 1) {
-            // one iteration of lag: the GPU always has the next iteration queued while the host looks at the count
             CK(cudaEventSynchronize(ev[(it - 1) & 1]));
             bound = m->h_n_active[1 + ((it - 1) & 1)]; // n_active only shrinks: a stale value is a valid bound
+            m->prof_layers = bound;
         }
     }
     CK(cudaStreamSynchronize(s));
@@ -714,6 +742,8 @@ rt_status rt_profile_reset(rt_model* m, int enable_timing)
     prof_collect(m);
     std::fill(m->prof_ms.begin(), m->prof_ms.end(), 0.);
     std::fill(m->prof_launches.begin(), m->prof_launches.end(), 0);
+    std::fill(m->prof_flops.begin(), m->prof_flops.end(), 0.);
+    std::fill(m->prof_bytes.begin(), m->prof_bytes.end(), 0.);
     m->prof_timing = enable_timing != 0;
     m->iters_enqueued = 0;
     return RT_OK;
@@ -734,6 +764,40 @@ rt_status rt_profile_get(rt_model* m, int cap, const char** names, double* ms, l
 }
 
 long long rt_iterations_enqueued(const rt_model* m) { return m ? m->iters_enqueued : 0; }
+long long rt_launch_count(void) { return g_rt_launches; }
+
+rt_status rt_profile_get_work(rt_model* m, int cap, double* flops, double* bytes)
+{
+    if (!m) return RT_ERR_INVALID;
+    const int k = (int)std::min<size_t>(cap, m->prof_names.size());
+    for (int i = 0; i < k; i++) {
+        if (flops) flops[i] = m->prof_flops[i];
+        if (bytes) bytes[i] = m->prof_bytes[i];
+    }
+    return RT_OK;
+}
+
+rt_status rt_timer_begin(rt_model* m)
+{
+    if (!m) return RT_ERR_INVALID;
+    CK(cudaSetDevice(m->device));
+    for (int i = 0; i < 2; i++)
+        if (!m->timer_ev[i]) CK(cudaEventCreate(&m->timer_ev[i]));
+    CK(cudaStreamSynchronize(m->stream));
+    CK(cudaEventRecord(m->timer_ev[0], m->stream));
+    return RT_OK;
+}
+
+rt_status rt_timer_end(rt_model* m, double* ms)
+{
+    if (!m || !ms || !m->timer_ev[0]) return RT_ERR_INVALID;
+    CK(cudaEventRecord(m->timer_ev[1], m->stream));
+    CK(cudaEventSynchronize(m->timer_ev[1]));
+    float f = 0.f;
+    CK(cudaEventElapsedTime(&f, m->timer_ev[0], m->timer_ev[1]));
+    *ms = f;
+    return RT_OK;
+}
 
 } // extern "C"
 

@@ -91,9 +91,15 @@ struct rt_model {
     std::vector<std::string> prof_names;
     std::vector<double> prof_ms;
     std::vector<long long> prof_launches;
-    std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_pending;
+    std::vector<double> prof_flops, prof_bytes; // algorithmic work of the launches, summed over the layers they process
+    struct ProfPending { int cls; cudaEvent_t a, b; };
+    std::vector<ProfPending> prof_pending;
     std::vector<cudaEvent_t> ev_pool;
+    int prof_layers = 0;           // layers the launches enqueued now process (set by the drivers in rt_api.cu)
+    cudaEvent_t timer_ev[2] = {nullptr, nullptr};
 };
+
+extern long long g_rt_launches; // every kernel launch of the library (bench.py gpu_launches)
 
 // ---- kernel launchers (each returns after enqueueing on `s`) -------------------------------------------------
 // layers processed = active[0 .. min(*n_active, nlay_bound))
@@ -116,5 +122,6 @@ void launch_intensity_single(const DevModel& d, cudaStream_t s, int lay, int up,
 
 // profiling hooks used by the launchers
 int rt_prof_class(rt_model* m, const char* name);
-void rt_prof_begin(rt_model* m, int cls, cudaStream_t s);
+// flops / bytes: ALGORITHMIC work per layer of this launch (DESIGN.md section "Kernels"); multiplied by m->prof_layers
+void rt_prof_begin(rt_model* m, int cls, cudaStream_t s, double flops_per_layer = 0., double bytes_per_layer = 0.);
 void rt_prof_end(rt_model* m, int cls, cudaStream_t s);

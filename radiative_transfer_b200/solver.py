@@ -18,12 +18,14 @@ from . import abi
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "librt_b200.so")
 _lib = None
+ABI_VERSION = 1
 
 ENTRY_POINTS = [
     "rt_params_default", "rt_status_string", "rt_last_error", "rt_abi_version", "rt_model_create", "rt_model_destroy",
     "rt_cloud_upload", "rt_boundary_populations", "rt_step", "rt_assemble", "rt_intensity", "rt_solve",
     "rt_calc_molecular_populations", "rt_solve_device", "rt_get_status", "rt_get_populations", "rt_set_populations",
-    "rt_profile_reset", "rt_profile_get", "rt_iterations_enqueued", "rt_maser_postpass",
+    "rt_profile_reset", "rt_profile_get", "rt_iterations_enqueued", "rt_maser_postpass", "rt_cloud_rebuild",
+    "rt_profile_get_work", "rt_launch_count", "rt_timer_begin", "rt_timer_end", "rt_device_fp64_peak",
 ]
 
 
@@ -47,6 +49,7 @@ def lib():
         L.rt_last_error.argtypes = [C.c_void_p]
         L.rt_iterations_enqueued.restype = C.c_longlong
         L.rt_iterations_enqueued.argtypes = [C.c_void_p]
+        L.rt_launch_count.restype = C.c_longlong
         _lib = L
     return _lib
 
@@ -187,10 +190,38 @@ class Model:
         self._ck(self.L_.rt_profile_reset(self.h, int(timing)), "rt_profile_reset")
 
     def profile_get(self):
+        """{kernel class: dict(ms, launches, flops, bytes)}; flops / bytes are ALGORITHMIC."""
         cap = 64
         names = (C.c_char_p * cap)(); ms = (C.c_double * cap)(); ln = (C.c_longlong * cap)(); n = C.c_int()
+        fl = (C.c_double * cap)(); by = (C.c_double * cap)()
         self._ck(self.L_.rt_profile_get(self.h, cap, names, ms, ln, C.byref(n)), "rt_profile_get")
-        return {names[i].decode(): (ms[i], ln[i]) for i in range(n.value)}
+        self._ck(self.L_.rt_profile_get_work(self.h, cap, fl, by), "rt_profile_get_work")
+        return {names[i].decode(): dict(ms=ms[i], launches=ln[i], flops=fl[i], bytes=by[i]) for i in range(n.value)}
+
+    def cloud_rebuild(self):
+        self._ck(self.L_.rt_cloud_rebuild(self.h), "rt_cloud_rebuild")
+
+    def timer_begin(self):
+        self._ck(self.L_.rt_timer_begin(self.h), "rt_timer_begin")
+
+    def timer_end(self) -> float:
+        ms = C.c_double()
+        self._ck(self.L_.rt_timer_end(self.h, C.byref(ms)), "rt_timer_end")
+        return ms.value
 
     def iterations_enqueued(self) -> int:
         return int(self.L_.rt_iterations_enqueued(self.h))
+
+
+def device_fp64_peak(device: int = 0, reps: int = 3):
+    """(DFMA TFLOP/s, DMMA TFLOP/s) measured on `device` by the library's microbenchmark kernels."""
+    a = C.c_double(); b = C.c_double()
+    rc = lib().rt_device_fp64_peak(int(device), int(reps), C.byref(a), C.byref(b))
+    if rc != abi.RT_OK:
+        raise RtError(f"rt_device_fp64_peak: {lib().rt_status_string(rc).decode()}")
+    return a.value, b.value
+
+
+def launch_count() -> int:
+    """Kernels launched by librt_b200.so in this process so far."""
+    return int(lib().rt_launch_count())

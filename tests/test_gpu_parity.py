@@ -1,0 +1,235 @@
+"""GPU (B200): the CUDA path, called through the C ABI (librt_b200.so via radiative_transfer_b200.solver.Model), against
+(1) the committed golden vectors of the unmodified reference, (2) the oracle run live on the same seeded inputs,
+(3) size-independent properties at BASELINE.json's full sizes.  Tolerances (north_star): populations 1e-6 relative
+on levels above 1e-30, iteration counts +-1, same convergence flags; single-step quantities far tighter."""
+import copy
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import golden_cases as G
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+CASES = list(G.CASES)
+
+
+@pytest.fixture(scope="module")
+def solver_mod():
+    import torch
+    assert torch.cuda.is_available(), "the gpu-marked tests need a CUDA device"
+    from radiative_transfer_b200 import solver
+    return solver
+
+
+def gpu_compute(solver, p):
+    """The same quantities as golden_cases.compute, from the CUDA library."""
+    m = solver.Model(p)
+    out = {}
+    out["boundary"] = m.boundary_layer_populations()
+    gold_b = None
+    return m, out
+
+
+@pytest.fixture(scope="module")
+def gpu_results(solver_mod):
+    cache = {}
+
+    def get(case):
+        if case in cache:
+            return cache[case]
+        p = G.problem(case)
+        gold = G.load(case)
+        assert G.problem_digest(p) == bytes(gold["digest"]).decode()
+        m = solver_mod.Model(p)
+        got = {}
+        got["boundary"] = m.boundary_layer_populations()
+        b = gold["boundary"]  # single-step quantities are evaluated on the reference's own start vector
+        M, got["df"] = m.assemble(b)
+        got.update(G.project("M", M))
+        got["step_pop"], got["step_eq"] = m.calc_new_pop(b)
+        got["intensity"] = np.array([m.intensity_calc(p.L - 1, u, l, b[p.L - 1]) for u, l in zip(gold["int_up"], gold["int_low"])])
+        pop, st = m.calculate_populations()
+        got["solve_pop"], got["solve_iters"], got["solve_conv"] = pop, st["iters"].copy(), st["converged"].copy()
+        post = m.maser_postpass(b, gold["post_up"], gold["post_low"])
+        for k, v in post.items():
+            got["post_" + k] = v
+        from radiative_transfer_b200 import abi
+        cp, cst = m.calc_molecular_populations(start_mode=abi.RT_START_CHAINED)
+        got["chain_pop"], got["chain_iters"], got["chain_conv"] = cp, cst["iters"].copy(), cst["converged"].copy()
+        m.close()
+        cache[case] = (p, gold, got)
+        return cache[case]
+    return get
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_golden_matrix_and_residual(gpu_results, case):
+    p, gold, got = gpu_results(case)
+    for k in gold:
+        if k == "M" or k.startswith("M_"):
+            scale = np.max(np.abs(gold[k]), axis=-1, keepdims=True) + 1e-300
+            assert np.max(np.abs(got[k] - gold[k]) / scale) < 1e-11, k
+    assert np.max(np.abs(got["df"] - gold["df"])) < 1e-11 * max(1.0, np.max(np.abs(gold["df"])))
+    assert rel_err(got["intensity"], gold["intensity"], 1e-300) < 1e-11
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_golden_boundary_and_step(gpu_results, case):
+    p, gold, got = gpu_results(case)
+    assert rel_err(got["boundary"], gold["boundary"], 1e-30) < 1e-7
+    assert rel_err(got["step_pop"], gold["step_pop"], 1e-30) < 1e-6
+    assert rel_err(got["step_eq"], gold["step_eq"], 0.0) < 1e-8
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_golden_converged_populations(gpu_results, case):
+    p, gold, got = gpu_results(case)
+    assert np.array_equal(got["solve_conv"], gold["solve_conv"])
+    conv = gold["solve_conv"] == 1
+    assert np.all(np.abs(got["solve_iters"] - gold["solve_iters"])[conv] <= 1)
+    assert rel_err(got["solve_pop"][conv], gold["solve_pop"][conv], 1e-30) < 1e-6
+    assert np.all(got["solve_iters"][~conv] == gold["solve_iters"][~conv])  # iteration cap
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_golden_chained_start_and_retry(gpu_results, case):
+    p, gold, got = gpu_results(case)
+    assert np.array_equal(got["chain_conv"], gold["chain_conv"])
+    conv = gold["chain_conv"] == 1
+    assert np.all(np.abs(got["chain_iters"] - gold["chain_iters"])[conv] <= 1)
+    assert rel_err(got["chain_pop"][conv], gold["chain_pop"][conv], 1e-30) < 1e-6
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_golden_maser_postpass(gpu_results, case):
+    p, gold, got = gpu_results(case)
+    for k in ("post_inv", "post_gain", "post_scalars", "post_tau_vs_aspect", "post_tau_vs_freq"):
+        scale = np.max(np.abs(gold[k])) + 1e-300
+        assert np.max(np.abs(got[k] - gold[k])) / scale < 1e-10, k
+
+
+# ---- live against the oracle, other sizes / seeds ---------------------------------------------------------------
+@pytest.mark.parametrize("name,L", [("generic", 9), ("oh", 5), ("oh_overlap", 5), ("ch3oh_small", 8), ("ch3oh_mid", 4),
+                                    ("h2o_small", 3)])
+def test_live_solve_vs_oracle(solver_mod, best_checker, problems, name, L):
+    p = problems(name, L)
+    m = solver_mod.Model(p)
+    pop, st = m.calculate_populations()
+    m.close()
+    pop_o, st_o, _ = best_checker.solve(p, nthreads=8)
+    assert np.array_equal(st["converged"], st_o["converged"])
+    conv = st_o["converged"] == 1
+    assert np.all(np.abs(st["iters"] - st_o["iters"])[conv] <= 1)
+    assert rel_err(pop[conv], pop_o[conv], 1e-30) < 1e-6
+    assert np.allclose(pop.sum(axis=1), 1.0, atol=1e-9)
+
+
+def test_retry_policy_non_methanol(solver_mod, best_checker, problems):
+    """radiative_transfer.cpp:259-276: accelerated failure -> un-accelerated retry from a fresh start (not CH3OH)."""
+    p = problems("h2o_small", 3)
+    m = solver_mod.Model(p)
+    pop, st = m.calc_molecular_populations(acceleration=True)
+    m.close()
+    pop_o, st_o, _ = best_checker.solve(p, retry=True, nthreads=8)
+    assert np.array_equal(st["converged"], st_o["converged"])
+    conv = st_o["converged"] == 1
+    assert np.all(np.abs(st["iters"] - st_o["iters"])[conv] <= 1)
+    assert rel_err(pop[conv], pop_o[conv], 1e-30) < 1e-6
+
+
+def test_given_start_and_iteration_cap(solver_mod, best_checker, problems):
+    """RT_START_GIVEN; a cap of 3 iterations returns the best-residual vector (iteration_control.h:105-109,128-135)."""
+    from radiative_transfer_b200 import abi
+    p = problems("ch3oh_small", 4)
+    start = best_checker.boltzmann(p)
+    m = solver_mod.Model(p)
+    pop, st = m.calculate_populations(pop0=start, max_iter=3)
+    m.close()
+    pop_o, st_o, _ = best_checker.solve(p, start_mode=abi.RT_START_GIVEN, pop0=start, max_iter=3)
+    assert np.all(st["iters"] == 3) and np.all(st["converged"] == 0)
+    assert np.array_equal(st_o["iters"], st["iters"])
+    assert rel_err(pop, pop_o, 1e-30) < 1e-7
+    assert rel_err(st["eq_error"], st_o["eq_error"], 0.0) < 1e-6
+
+
+def test_single_layer_and_layer_independence(solver_mod, problems):
+    """A layer's answer does not depend on which other layers are in the batch: bitwise."""
+    p = problems("ch3oh_small", 8)
+    m = solver_mod.Model(p)
+    pop, st = m.calculate_populations()
+    m.close()
+    for lo, hi in ((0, 1), (3, 6), (7, 8)):
+        q = p.sliced(lo, hi)
+        m2 = solver_mod.Model(q)
+        pop2, st2 = m2.calculate_populations()
+        m2.close()
+        assert np.array_equal(pop2, pop[lo:hi])
+        assert np.array_equal(st2["iters"], st["iters"][lo:hi])
+
+
+def test_error_paths(solver_mod, problems):
+    from radiative_transfer_b200 import abi
+    p = problems("generic", 2)
+    m = solver_mod.Model(p, upload_cloud=False)
+    with pytest.raises(solver_mod.RtError, match="no cloud"):
+        m.calculate_populations()
+    q = copy.copy(p)
+    q.layers = dict(p.layers)
+    s, hold = q.layer_soa()
+    s.dust_ncomp = 2  # iteration_lvg.cpp:81-84: exit(1) in the reference, a status code here
+    rc = m.L_.rt_cloud_upload(m.h, C.byref(s))
+    assert rc == 4
+    m.close()
+
+
+# ---- BASELINE.json full sizes: size-independent properties -------------------------------------------------------
+def test_full_size_ch3oh_properties(solver_mod, best_checker):
+    """Config 2 (CH3OH-A, N = 768, L = 200): normalisation, fixed-point property, layer independence, and parity
+    with the oracle on a bounded sample of layers."""
+    from radiative_transfer_b200 import synthetic
+    p = synthetic.config_ch3oh(L=200)
+    m = solver_mod.Model(p)
+    pop, st = m.calculate_populations()
+    assert pop.shape == (200, 768)
+    assert np.allclose(pop.sum(axis=1), 1.0, atol=1e-9)
+    assert np.all(pop > -1e-12)
+    conv = st["converged"] == 1
+    assert conv.mean() > 0.9
+    # fixed point: one more calc_new_pop moves a converged layer by less than the stop criterion allows
+    new, eq = m.calc_new_pop(pop)
+    rel = np.max(np.abs(new - pop) / (pop + 1e-99), axis=1)
+    assert np.all(rel[conv] < 1e-5)
+    m.close()
+    sample = [0, 97, 199]
+    for l in sample:
+        q = p.sliced(l, l + 1)
+        m1 = solver_mod.Model(q)
+        pop1, st1 = m1.calculate_populations()
+        m1.close()
+        assert np.array_equal(pop1[0], pop[l]) and st1["iters"][0] == st["iters"][l]
+    q = p.sliced(97, 98)
+    pop_o, st_o, _ = best_checker.solve(q)
+    assert st_o["converged"][0] == st["converged"][97]
+    assert abs(int(st_o["iters"][0]) - int(st["iters"][97])) <= 1
+    assert rel_err(pop[97], pop_o[0], 1e-30) < 1e-6
+
+
+def test_full_size_oh_overlap_properties(solver_mod, best_checker):
+    """Config 3 (OH with hyperfine overlap, N = 56, L = 400, un-accelerated): sample of layers against the oracle."""
+    from radiative_transfer_b200 import synthetic
+    p = synthetic.config_oh(L=400, overlap=True)
+    m = solver_mod.Model(p)
+    pop, st = m.calculate_populations()
+    m.close()
+    assert np.allclose(pop.sum(axis=1), 1.0, atol=1e-9)
+    idx = [0, 133, 266, 399]
+    for l in idx:
+        q = p.sliced(l, l + 1)
+        pop_o, st_o, _ = best_checker.solve(q)
+        assert st_o["converged"][0] == st["converged"][l]
+        if st_o["converged"][0]:
+            assert abs(int(st_o["iters"][0]) - int(st["iters"][l])) <= 1
+            assert rel_err(pop[l], pop_o[0], 1e-30) < 1e-6

@@ -1,0 +1,72 @@
+"""CPU, world_size 2, gloo: the N>1 host path (layer partition + ragged all_gather of populations / status).
+The rank-local solver is the oracle here (no GPU in this container); on the GPU box the same code runs over NCCL with
+radiative_transfer_b200.solver.Model as the rank-local solver (bench.py --mode shard, tests/test_gpu_parity.py)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, L, q):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from radiative_transfer_b200 import sharding, synthetic
+    from oracle.loader import Checker
+    chk = Checker("port")
+    p = synthetic.small("ch3oh_small", L=L)
+
+    def solve_fn(sub):
+        pop, st, _ = chk.solve(sub)
+        return pop, st
+    pop, st = sharding.solve_sharded(p, solve_fn, world, rank)
+    if rank == 0:
+        q.put((pop, st["iters"].copy(), st["converged"].copy()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("L", [5, 2])
+def test_sharded_equals_unsharded(L, port):
+    import torch.multiprocessing as mp
+    from radiative_transfer_b200 import synthetic
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    world, tcp = 2, _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, tcp, L, q)) for r in range(world)]
+    for pr in procs:
+        pr.start()
+    pop, iters, conv = q.get(timeout=180)
+    for pr in procs:
+        pr.join(timeout=60)
+        assert pr.exitcode == 0
+    p = synthetic.small("ch3oh_small", L=L)
+    pop1, st1, _ = port.solve(p)
+    assert np.array_equal(pop, pop1)  # layers are independent: bitwise
+    assert np.array_equal(iters, st1["iters"]) and np.array_equal(conv, st1["converged"])
+
+
+def test_layer_range_and_sweep_assign():
+    from radiative_transfer_b200 import sharding
+    for L in (1, 7, 200, 400):
+        for w in (1, 2, 3, 8):
+            r = [sharding.layer_range(L, w, k) for k in range(w)]
+            assert r[0][0] == 0 and r[-1][1] == L
+            assert all(r[k][1] == r[k + 1][0] for k in range(w - 1))
+            sizes = [b - a for a, b in r]
+            assert max(sizes) - min(sizes) <= 1
+    pts = sorted(sum((sharding.sweep_assign(512, 8, k) for k in range(8)), []))
+    assert pts == list(range(512))
