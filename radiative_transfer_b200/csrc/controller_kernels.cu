@@ -286,8 +286,13 @@ __global__ void k_set_rhs(DevModel d, int nlay_bound)
     const int a = blockIdx.y;
     if (a >= nlay_bound || a >= *d.n_active) return;
     const int lay = d.active[a];
+    // b = e0 rides as column Np of the matrix; columns Np+1 .. ld-1 are zero padding
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < d.Np) d.rhs[(size_t)lay * d.Np + i] = (i == 0) ? 1. : 0.;
+    if (i < d.Np) {
+        double* row = d.Mmat + ((size_t)lay * d.Np + i) * d.ld + d.Np;
+        row[0] = (i == 0) ? 1. : 0.;
+        for (int c = 1; c < d.ld - d.Np; c++) row[c] = 0.;
+    }
 }
 
 // matrix[0][i] = 1 (boundary_layer_populations, iteration_control.cpp:81-83); padded columns stay 0
@@ -297,7 +302,7 @@ __global__ void k_set_row0(DevModel d, int nlay_bound)
     if (a >= nlay_bound || a >= *d.n_active) return;
     const int lay = d.active[a];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < d.Np) d.Mmat[(size_t)lay * d.Np * d.Np + i] = (i < d.N) ? 1. : 0.;
+    if (i < d.Np) d.Mmat[(size_t)lay * d.Np * d.ld + i] = (i < d.N) ? 1. : 0.;
 }
 
 __global__ void k_copy_rhs_to_pop(DevModel d, int nlay_bound)

@@ -81,13 +81,13 @@ __device__ __forceinline__ void rate_electrons(const DevModel& d, int lay, int u
 // grid (ceil(N/32), ceil(N/32), L), block (32, 8): tile (bi, bj) of the lower triangle; writes C[i][j] = up-rate
 // j->i and, through a shared-memory transpose, C[j][i] = down-rate i->j, both as coalesced row segments.
 // half_A != 0: boundary_layer_populations variant (iteration_control.cpp:72-78): neutrals only, + 0.5*A_ul.
-__global__ void __launch_bounds__(256) k_coll_offdiag(DevModel d, double* __restrict__ out, int half_A,
+__global__ void __launch_bounds__(256) k_coll_offdiag(DevModel d, double* __restrict__ out, int ldo, int half_A,
                                                       const double* __restrict__ einst)
 {
     const int bi = blockIdx.y, bj = blockIdx.x, lay = blockIdx.z;
     if (bj > bi) return;
     __shared__ double s_down[32][33];
-    double* C = out + (size_t)lay * d.Np * d.Np;
+    double* C = out + (size_t)lay * d.Np * ldo;
     const int tx = threadIdx.x, ty = threadIdx.y;
     for (int r = ty; r < 32; r += 8) {
         const int i = bi * 32 + r, j = bj * 32 + tx;
@@ -101,45 +101,46 @@ __global__ void __launch_bounds__(256) k_coll_offdiag(DevModel d, double* __rest
                 up += b;
             }
             else down = 0.5 * einst[(size_t)i * d.N + j] + down;
-            C[(size_t)i * d.Np + j] = up;
+            C[(size_t)i * ldo + j] = up;
         }
         s_down[r][tx] = down;
     }
     __syncthreads();
     for (int r = ty; r < 32; r += 8) {
         const int j = bj * 32 + r, i = bi * 32 + tx; // transposed: row j, column i
-        if (i < d.N && j < i) C[(size_t)j * d.Np + i] = s_down[tx][r];
+        if (i < d.N && j < i) C[(size_t)j * ldo + i] = s_down[tx][r];
     }
 }
 
 // Diagonal = -(sum of the other entries of the column) (iteration_lvg.cpp:127-131: every rate leaves its source
 // level through the diagonal of the source column); padding block = identity.  One thread per column, coalesced.
-__global__ void k_coll_diag(DevModel d, double* __restrict__ out)
+__global__ void k_coll_diag(DevModel d, double* __restrict__ out, int ldo)
 {
     const int lay = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= d.Np) return;
-    double* C = out + (size_t)lay * d.Np * d.Np;
+    double* C = out + (size_t)lay * d.Np * ldo;
     if (i >= d.N) {
-        for (int r = 0; r < d.Np; r++) C[(size_t)r * d.Np + i] = (r == i) ? 1. : 0.;
+        for (int r = 0; r < d.Np; r++) C[(size_t)r * ldo + i] = (r == i) ? 1. : 0.;
         return;
     }
     double s = 0.;
     for (int r = 0; r < d.N; r++)
-        if (r != i) s += C[(size_t)r * d.Np + i];
-    C[(size_t)i * d.Np + i] = -s;
-    for (int r = d.N; r < d.Np; r++) C[(size_t)r * d.Np + i] = 0.;
+        if (r != i) s += C[(size_t)r * ldo + i];
+    C[(size_t)i * ldo + i] = -s;
+    for (int r = d.N; r < d.Np; r++) C[(size_t)r * ldo + i] = 0.;
 }
 
 void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int half_A)
 {
+    const int ldo = (out == d.Mmat) ? d.ld : d.Np; // the boundary-start variant assembles straight into Mmat
     const int nt = (d.N + 31) / 32;
     dim3 grid(nt, nt, d.L), block(32, 8);
     g_rt_launches++;
-    k_coll_offdiag<<<grid, block, 0, s>>>(d, out, half_A, d.einst);
+    k_coll_offdiag<<<grid, block, 0, s>>>(d, out, ldo, half_A, d.einst);
     dim3 g2((d.Np + 127) / 128, d.L);
     g_rt_launches++;
-    k_coll_diag<<<g2, 128, 0, s>>>(d, out);
+    k_coll_diag<<<g2, 128, 0, s>>>(d, out, ldo);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -215,8 +216,9 @@ __global__ void __launch_bounds__(ASM_WARPS * 32) k_assemble(DevModel d, int nla
     const int row = blockIdx.x * ASM_WARPS + warp;
     if (row >= Np) return;
     const double* __restrict__ Crow = d.Cmat + ((size_t)lay * Np + row) * Np;
-    double* __restrict__ Mrow = d.Mmat + ((size_t)lay * Np + row) * Np;
-    if (lane == 0) d.rhs[(size_t)lay * Np + row] = (row == 0) ? 1. : 0.; // b = e0, iteration_lvg.cpp:97-98
+    double* __restrict__ Mrow = d.Mmat + ((size_t)lay * Np + row) * d.ld;
+    // b = e0 (iteration_lvg.cpp:97-98) rides as column Np; columns Np+1 .. ld-1 are zero padding
+    if (lane < d.ld - Np) Mrow[Np + lane] = (lane == 0 && row == 0) ? 1. : 0.;
     double dot = 0.;
     if (row == 0) {
         // normalisation row, iteration_lvg.cpp:149-151; padded columns stay 0

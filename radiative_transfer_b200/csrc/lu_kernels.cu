@@ -4,274 +4,493 @@
 // call site iteration_lvg.cpp:97-101): LU with ROW PARTIAL PIVOTING (largest |a_ik| of the column, first
 // occurrence wins), multipliers l = a_ik * (1/pivot), right-hand side eliminated on the fly, back substitution.
 //
-// Blocked right-looking algorithm on the padded [Np][Np] row-major matrices in HBM, panel width NB = 32:
-//   for each panel k:  k_panel  : factor the (Np-32k) x 32 panel in shared memory (pivot search, row swaps,
-//                                 rank-1 updates; the rhs rides along as a 33rd column), swap the trailing rows
-//                      k_trsm   : U12 = L11^-1 A12                       (32 x m, unit lower triangular solve)
-//                      k_gemm   : A22 -= L21 * U12                        (m x m x 32, the O(N^3) part)
-//   k_backsolve: U x = y, blocked from the bottom.
-// Work per layer: (2/3) Np^3 + O(Np^2) flop; HBM traffic ~ sum over panels of 16 m^2 bytes.
+// Layout: Mmat [L][Np][ld] row-major, ld = Np + 32; column Np is the right-hand side (so the forward substitution
+// is just one more column of every update), columns Np+1.. are zero padding.
+//
+// Two-level blocked right-looking algorithm, inner panel 32 columns, outer block 64 columns:
+//   for every outer block at k0:
+//     k_panel (k0)        factor the (Np-k0) x 32 panel, REGISTER-resident (each thread owns up to 3 rows x 32
+//                         columns), pivot search by warp shuffles; records the composed row permutation
+//     k_trsm  (k0, mode 1) columns right of the panel: apply the permutation, U1 = L11^-1 A
+//     k_gemm  (K = 32)    update only the next 32 columns (the second panel of the block)
+//     k_panel (k0+32)     second panel; also permutes the L block of the first panel (LAPACK-style) so that
+//     k_trsm  (k0+32, mode 2) rows k0+32..k0+63 of the columns right of the block: permutation, -= L21 U1, L22^-1
+//     k_gemm  (K = 64)    trailing update A22 -= [L1 L2] [U1; U2] on FP64 tensor cores (DMMA mma.sync m8n8k4):
+//                         the O(N^3) part; 8 flop per byte of trailing matrix moved instead of 4 at K = 32
+//   k_backsolve           U x = y, blocked from the bottom.
+// Work per layer: (2/3) Np^3 + O(Np^2) flop; HBM traffic ~ sum over outer blocks of 16 m^2 bytes.
 #include "rt_internal.h"
 #include <cfloat>
 
-#define PNL_THREADS 256
-#define LU_PANEL_SMEM_MAX (226 * 1024) // 227 KB per CTA minus the kernel's static shared memory
-#define PNL_LD 33 // 32 panel columns + rhs column; odd stride -> conflict-free column access
+#define PNL_MAXROWS 768 // largest panel height = largest Np
+#ifndef PNL_BIG_R
+#define PNL_BIG_R 3     // rows per thread x threads of the kernel variant for 512 < m <= 768
+#define PNL_BIG_NT 256
+#endif
+#ifndef PNL_JB
+#define PNL_JB 8   // columns per unrolled block of the panel's column loop
+#endif
 
-__global__ void __launch_bounds__(PNL_THREADS) k_panel(DevModel d, int k, int nlay_bound)
+// ------------------------------------------------------------------------------------------------------------
+// Panel factorisation.  Local row r = t + 256 i (i < R) lives in registers x[i][0..31] of thread t.
+// Per column j: (1) arg-max |x[.][j]| over rows >= j (ties -> smallest row, like the scalar loop), two-stage
+// reduction with ONE barrier; (2) the owners of rows j and p exchange their rows through shared memory, every
+// thread reads the pivot row (broadcast) -- second barrier; (3) rank-1 update in registers.
+// Shared buffers are double-buffered by the parity of j, so two barriers per column suffice.
+// ------------------------------------------------------------------------------------------------------------
+template <int R, int NT>
+__global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int nlay_bound)
 {
     const int a = blockIdx.x;
     if (a >= nlay_bound || a >= *d.n_active) return;
     const int lay = d.active[a];
-    const int Np = d.Np, k0 = k * RT_NB, m = Np - k0;
-    extern __shared__ double P[]; // [m][PNL_LD]
-    __shared__ int s_piv[RT_NB];
-    __shared__ double s_val[PNL_THREADS / 32];
-    __shared__ int s_idx[PNL_THREADS / 32];
-    double* __restrict__ A = d.Mmat + (size_t)lay * Np * Np;
-    double* __restrict__ b = d.rhs + (size_t)lay * Np;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int Np = d.Np, ld = d.ld, m = Np - k0;
+    double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
 
-    for (int r = warp; r < m; r += PNL_THREADS / 32) P[r * PNL_LD + lane] = A[(size_t)(k0 + r) * Np + k0 + lane];
-    for (int r = tid; r < m; r += PNL_THREADS) P[r * PNL_LD + 32] = b[k0 + r];
+    extern __shared__ double s_tile[]; // [m][33]: coalesced staging of the panel on the way in and out
+    __shared__ double s_val[2][NT / 32];
+    __shared__ int s_idx[2][NT / 32];
+    __shared__ __align__(16) double s_prow[2][32]; // pivot row (all 32 columns)
+    __shared__ int s_pos[64], s_cur[64], s_naff, s_own[2];   // composed permutation (see k_trsm)
+    __shared__ short s_slot[NT * R]; // local row -> slot in s_pos, -1 = untouched
+
+    for (int r = warp; r < m; r += NT / 32) s_tile[r * 33 + lane] = A[(size_t)(k0 + r) * ld + k0 + lane];
+    for (int r = t; r < m; r += NT) s_slot[r] = (short)(r < 32 ? r : -1);
+    if (t < 32) { s_pos[t] = t; s_cur[t] = t; }
+    if (t == 0) s_naff = 32;
     __syncthreads();
 
-    for (int j = 0; j < RT_NB; j++) {
-        // ---- pivot search: max |P[r][j]|, r >= j; ties -> smallest r (first occurrence, as the scalar loop)
-        double best = -1.;
-        int bidx = 0x7fffffff;
-        for (int r = j + tid; r < m; r += PNL_THREADS) {
-            const double v = fabs(P[r * PNL_LD + j]);
-            if (v > best) { best = v; bidx = r; } // r ascending per thread: strict '>' keeps the first
-        }
+    // Rows never move between threads: vp[i] is the CURRENT position of the row held in x[i] (the position the
+    // scalar algorithm's interchanges would have put it at), -1 for padding slots.  x[i][c] holds column jb + c of
+    // the row, jb = first column of the current block of PNL_JB columns: the column loop is unrolled over one
+    // block only (register indices must be static; fully unrolling 32 columns gives 430 KB of straight-line code
+    // that stalls on instruction fetch) and the registers are shifted left by PNL_JB after every block.
+    // Finished entries (multipliers, pivot rows) go to the staging tile row of the thread's ORIGINAL row.
+    double x[R][32];
+    int vp[R];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double ov = __shfl_xor_sync(0xffffffffu, best, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
-            if (ov > best || (ov == best && oi < bidx)) { best = ov; bidx = oi; }
-        }
-        if (lane == 0) { s_val[warp] = best; s_idx[warp] = bidx; }
-        __syncthreads();
-        if (warp == 0) {
-            best = lane < PNL_THREADS / 32 ? s_val[lane] : -1.;
-            bidx = lane < PNL_THREADS / 32 ? s_idx[lane] : 0x7fffffff;
+    for (int i = 0; i < R; i++) {
+        const int r = t + NT * i;
+        vp[i] = r < m ? r : -1;
 #pragma unroll
-            for (int o = 4; o > 0; o >>= 1) {
+        for (int c = 0; c < 32; c++) x[i][c] = r < m ? s_tile[r * 33 + c] : 0.;
+    }
+
+#pragma unroll 1
+    for (int jb = 0; jb < 32; jb += PNL_JB) {
+#pragma unroll
+        for (int jj = 0; jj < PNL_JB; jj++) {
+            const int j = jb + jj;
+            const int buf = jj & 1;
+            // ---- (1) pivot search over the rows at positions >= j; ties -> smallest position
+            double best = -1.;
+            int bidx = 0x7fffffff;
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                if (vp[i] >= j) {
+                    const double v = fabs(x[i][jj]);
+                    if (v > best || (v == best && vp[i] < bidx)) { best = v; bidx = vp[i]; }
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
                 const double ov = __shfl_xor_sync(0xffffffffu, best, o);
                 const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
                 if (ov > best || (ov == best && oi < bidx)) { best = ov; bidx = oi; }
             }
-            if (lane == 0) s_piv[j] = (bidx == 0x7fffffff) ? j : bidx; // all-NaN column: keep the diagonal
-        }
-        __syncthreads();
-        const int p = s_piv[j];
-        if (p != j && tid < PNL_LD) {
-            const double t = P[j * PNL_LD + tid];
-            P[j * PNL_LD + tid] = P[p * PNL_LD + tid];
-            P[p * PNL_LD + tid] = t;
-        }
-        __syncthreads();
-        const double piv = P[j * PNL_LD + j];
-        if (piv != 0.) {
+            if (lane == 0) { s_val[buf][warp] = best; s_idx[buf][warp] = bidx; }
+            __syncthreads();
+            best = s_val[buf][0];
+            bidx = s_idx[buf][0];
+#pragma unroll
+            for (int w = 1; w < NT / 32; w++) {
+                const double ov = s_val[buf][w];
+                const int oi = s_idx[buf][w];
+                if (ov > best || (ov == best && oi < bidx)) { best = ov; bidx = oi; }
+            }
+            const int p = (bidx == 0x7fffffff) ? j : bidx; // all-NaN column: keep the diagonal
+            // ---- (2) interchange of positions j <-> p: the pivot row is published, nothing else moves
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                if (vp[i] == p) {
+                    double2* pr = reinterpret_cast<double2*>(s_prow[buf]);
+#pragma unroll
+                    for (int c = 0; c < 16; c++) pr[c] = make_double2(x[i][2 * c], x[i][2 * c + 1]);
+                    s_own[buf] = t + NT * i;
+                    vp[i] = j;
+                }
+                else if (vp[i] == j) vp[i] = p;
+            }
+            if (t == 0 && p != j) {
+                // bookkeeping of the composed permutation: s_cur[slot] = slot of the ORIGINAL row now at s_pos[slot]
+                int sp = s_slot[p];
+                if (sp < 0) { sp = s_naff++; s_pos[sp] = p; s_cur[sp] = sp; s_slot[p] = (short)sp; }
+                const int tmp = s_cur[j]; s_cur[j] = s_cur[sp]; s_cur[sp] = tmp;
+            }
+            __syncthreads();
+            // U part of the pivot row is final: into the owner's staging-tile row (columns j..31)
+            if (t >= jj && jb + t < 32) s_tile[s_own[buf] * 33 + jb + t] = s_prow[buf][t];
+            // ---- (3) rank-1 update of the rows below j
+            const double piv = s_prow[buf][jj];
             const double rp = 1. / piv;
-            for (int r = j + 1 + tid; r < m; r += PNL_THREADS) {
-                double* row = P + r * PNL_LD;
-                const double l = row[j] * rp;
-                if (l != 0.) {
-                    row[j] = l;
-                    const double* prow = P + j * PNL_LD;
-                    for (int c = j + 1; c <= RT_NB; c++) row[c] -= l * prow[c];
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                if (vp[i] > j) {
+                    double l = x[i][jj];
+                    if (piv != 0.) {
+                        l *= rp;
+                        if (l != 0.) {
+#pragma unroll
+                            for (int c = jj + 1; c < 32; c++) x[i][c] -= l * s_prow[buf][c];
+                        }
+                    }
+                    s_tile[(t + NT * i) * 33 + j] = l; // multiplier (or the untouched entry if piv == 0)
                 }
             }
         }
-        __syncthreads();
+        // shift the live columns to the front
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+#pragma unroll
+            for (int c = 0; c < 32 - PNL_JB; c++) x[i][c] = x[i][c + PNL_JB];
+#pragma unroll
+            for (int c = 32 - PNL_JB; c < 32; c++) x[i][c] = 0.;
+        }
     }
 
-    for (int r = warp; r < m; r += PNL_THREADS / 32) A[(size_t)(k0 + r) * Np + k0 + lane] = P[r * PNL_LD + lane];
-    for (int r = tid; r < m; r += PNL_THREADS) b[k0 + r] = P[r * PNL_LD + 32];
-    if (tid < RT_NB) d.ipiv[(size_t)lay * Np + k0 + tid] = k0 + s_piv[tid];
-    // row interchanges for the columns to the right of the panel: columns are independent, so each thread
-    // replays the 32 swaps in order for its own columns (coalesced across the warp for every row touched)
-    for (int c = k0 + RT_NB + tid; c < Np; c += PNL_THREADS) {
-        for (int j = 0; j < RT_NB; j++) {
-            const int p = s_piv[j];
-            if (p != j) {
-                double* x = A + (size_t)(k0 + j) * Np + c;
-                double* y = A + (size_t)(k0 + p) * Np + c;
-                const double t = *x;
-                *x = *y;
-                *y = t;
-            }
+    // ---- write the factored panel back: row at final position vp <- staging-tile row of its owner (coalesced)
+    __shared__ short s_owner[NT * R];
+#pragma unroll
+    for (int i = 0; i < R; i++)
+        if (vp[i] >= 0) s_owner[vp[i]] = (short)(t + NT * i);
+    __syncthreads();
+    for (int r = warp; r < m; r += NT / 32) A[(size_t)(k0 + r) * ld + k0 + lane] = s_tile[s_owner[r] * 33 + lane];
+    const int naff = s_naff;
+    int* aff = d.lu_aff + ((size_t)lay * (Np / RT_NB) + k0 / RT_NB) * RT_AFF_STRIDE;
+    if (t == 0) aff[0] = naff;
+    if (t < 64) { aff[4 + t] = t < naff ? s_pos[t] : 0; aff[68 + t] = t < naff ? s_cur[t] : 0; }
+    // ---- LAPACK-style interchange of the `nleft` columns left of the panel (the L block of the first panel of
+    // this outer block): gather every affected row, barrier, scatter
+    if (nleft > 0) {
+        double v[8];
+        const int nel = naff * nleft; // <= 64 * 32
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int e = t + NT * q;
+            if (e < nel) { const int s = e / nleft, c = e - s * nleft; v[q] = A[(size_t)(k0 + s_pos[s_cur[s]]) * ld + k0 - nleft + c]; }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int e = t + NT * q;
+            if (e < nel) { const int s = e / nleft, c = e - s * nleft; if (s_cur[s] != s) A[(size_t)(k0 + s_pos[s]) * ld + k0 - nleft + c] = v[q]; }
         }
     }
 }
 
-// U12 = L11^-1 * A12: grid (column tiles of 128, layers).  L11 is the unit-lower 32x32 block the panel kernel left
-// in place.  Each thread owns one column of A12: loads it (coalesced across the CTA for every row), forward
-// substitution entirely in registers, stores it back.
+// ------------------------------------------------------------------------------------------------------------
+// Row permutation + triangular solve for the columns right of a panel.  One thread per column, 128 columns per
+// CTA.  The panel kernel left the COMPOSED permutation of its 32 interchanges: naff affected local rows
+// pos[0..naff) (pos[s] = s for s < 32, then the pivot rows taken from below) and cur[s] = slot of the original
+// row that ends at pos[s].  Rows displaced to below the block always come from the top 32.
+//   mode 1: x = rows k0..k0+31 (after the permutation);                       x <- L11^-1 x
+//   mode 2: same, but first  x -= Lleft * u,  Lleft = A[k0..k0+31][k0-32..k0-1] (L21 of the first panel of the
+//           outer block, already permuted by k_panel), u = U1 rows k0-32..k0-1 of the column
+// ------------------------------------------------------------------------------------------------------------
 #define TRSM_THREADS 128
-__global__ void __launch_bounds__(TRSM_THREADS) k_trsm(DevModel d, int k, int nlay_bound)
+#define TRSM_LDT 34 // even: rows of the transposed triangles stay 16-byte aligned for double2 loads
+__global__ void __launch_bounds__(TRSM_THREADS) k_trsm(DevModel d, int k0, int c0, int mode, int nlay_bound)
 {
     const int a = blockIdx.y;
     if (a >= nlay_bound || a >= *d.n_active) return;
     const int lay = d.active[a];
-    const int Np = d.Np, k0 = k * RT_NB;
-    __shared__ double Ls[32][33];
-    double* __restrict__ A = d.Mmat + (size_t)lay * Np * Np;
+    const int Np = d.Np, ld = d.ld;
+    __shared__ __align__(16) double Lt[32 * TRSM_LDT];  // Lt[q][r] = L[r][q] of the panel's unit-lower 32x32 block
+    __shared__ __align__(16) double Llt[32 * TRSM_LDT]; // mode 2: Llt[q][r] = A[k0+r][k0-32+q]
+    __shared__ int s_pos[64], s_cur[64];
+    double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
+    const int* aff = d.lu_aff + ((size_t)lay * (Np / RT_NB) + k0 / RT_NB) * RT_AFF_STRIDE;
+    const int naff = aff[0];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    for (int r = warp; r < 32; r += TRSM_THREADS / 32) Ls[r][lane] = A[(size_t)(k0 + r) * Np + k0 + lane];
+    for (int r = warp; r < 32; r += TRSM_THREADS / 32) {
+        Lt[lane * TRSM_LDT + r] = A[(size_t)(k0 + r) * ld + k0 + lane];
+        if (mode == 2) Llt[lane * TRSM_LDT + r] = A[(size_t)(k0 + r) * ld + k0 - 32 + lane];
+    }
+    if (tid < 64) { s_pos[tid] = aff[4 + tid]; s_cur[tid] = aff[68 + tid]; }
     __syncthreads();
-    const int c = k0 + RT_NB + blockIdx.x * TRSM_THREADS + tid;
-    if (c >= Np) return;
+    const int c = c0 + blockIdx.x * TRSM_THREADS + tid;
+    if (c >= ld) return;
+    // rows k0..k0+31 after the permutation: gathered straight from global memory (the same row for every thread of
+    // the CTA -> coalesced); all gathers precede the stores of this column, columns are independent
     double x[32];
 #pragma unroll
-    for (int r = 0; r < 32; r++) x[r] = A[(size_t)(k0 + r) * Np + c];
+    for (int r = 0; r < 32; r++) x[r] = A[(size_t)(k0 + s_pos[s_cur[r]]) * ld + c];
+    double u[32];
+    if (mode == 2) {
 #pragma unroll
-    for (int r = 1; r < 32; r++) {
-        double s = x[r];
+        for (int q = 0; q < 32; q++) u[q] = A[(size_t)(k0 - 32 + q) * ld + c];
+    }
+    // rows displaced below the block receive ORIGINAL top rows (still untouched in memory: they are rewritten last)
+    for (int s = 32; s < naff; s++)
+        if (s_cur[s] != s) A[(size_t)(k0 + s_pos[s]) * ld + c] = A[(size_t)(k0 + s_pos[s_cur[s]]) * ld + c];
+    if (mode == 2) {
+        // x -= Lleft * u: column sweep, 32 independent accumulators per step
 #pragma unroll
-        for (int q = 0; q < r; q++) s -= Ls[r][q] * x[q];
-        x[r] = s;
+        for (int q = 0; q < 32; q++) {
+            const double2* lq = reinterpret_cast<const double2*>(Llt + q * TRSM_LDT);
+#pragma unroll
+            for (int r2 = 0; r2 < 16; r2++) {
+                const double2 l = lq[r2];
+                x[2 * r2] -= l.x * u[q];
+                x[2 * r2 + 1] -= l.y * u[q];
+            }
+        }
+    }
+    // forward substitution, right-looking: after x[q] is final, every x[r], r > q, is updated independently
+#pragma unroll
+    for (int q = 0; q < 31; q++) {
+        const double2* lq = reinterpret_cast<const double2*>(Lt + q * TRSM_LDT);
+#pragma unroll
+        for (int r2 = (q + 1) / 2; r2 < 16; r2++) {
+            const double2 l = lq[r2];
+            if (2 * r2 > q) x[2 * r2] -= l.x * x[q];
+            x[2 * r2 + 1] -= l.y * x[q];
+        }
     }
 #pragma unroll
-    for (int r = 1; r < 32; r++) A[(size_t)(k0 + r) * Np + c] = x[r];
+    for (int r = 0; r < 32; r++) A[(size_t)(k0 + r) * ld + c] = x[r];
 }
 
-// A22 -= L21 * U12.  64 x 64 output tile per CTA, 256 threads, 4 x 4 register tile per thread, K = 32.
-#define GT 64
-__global__ void __launch_bounds__(256) k_gemm(DevModel d, int k, int nlay_bound)
+// ------------------------------------------------------------------------------------------------------------
+// Trailing update on the FP64 tensor cores:  C[i0.., c0..c1) -= A[i0.., kk0..kk0+K) * A[kk0..kk0+K, c0..c1),
+// K = 32 or 64.  CTA tile 128 x 64, 8 warps (4 x 2), warp tile 32 x 32 = 4 x 4 DMMA m8n8k4 tiles, accumulators
+// initialised with C (so the epilogue is a plain store of -(-C + AB) ... i.e. we accumulate D = C - A*B by feeding
+// the NEGATED A fragment).  A and B tiles are staged once in shared memory with cp.async (K <= 64: no k-loop
+// pipeline needed; two CTAs per SM overlap one CTA's loads with the other's math).
+// Shared-memory strides are = 4 (mod 16) doubles so that every fragment load is bank-conflict free:
+//   A fragment: lane holds As[row = lane/4][k = lane%4]   (row-major tile, stride K+4)
+//   B fragment: lane holds Bs[k = lane%4][col = lane/4]   (row-major tile, stride 68)
+// ------------------------------------------------------------------------------------------------------------
+#define GM_ROWS 128
+#define GM_COLS 64
+#define GM_LDB 68
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+template <int K>
+__global__ void __launch_bounds__(256, 2) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int nlay_bound)
 {
     const int a = blockIdx.z;
     if (a >= nlay_bound || a >= *d.n_active) return;
     const int lay = d.active[a];
-    const int Np = d.Np, k0 = k * RT_NB, t0 = k0 + RT_NB;
-    const int i0 = t0 + blockIdx.y * GT, j0 = t0 + blockIdx.x * GT;
-    __shared__ double As[RT_NB][GT + 1]; // As[q][i] = L21[i][q]  (transposed for conflict-free reads)
-    __shared__ double Bs[RT_NB][GT];     // Bs[q][j] = U12[q][j]
-    double* __restrict__ A = d.Mmat + (size_t)lay * Np * Np;
-    const int tid = threadIdx.x;
-    // load L21 tile: 64 rows x 32 cols
-    for (int e = tid; e < GT * RT_NB; e += 256) {
-        const int r = e >> 5, q = e & 31;
-        As[q][r] = (i0 + r < Np) ? A[(size_t)(i0 + r) * Np + k0 + q] : 0.;
+    const int Np = d.Np, ld = d.ld;
+    constexpr int LDA = K + 4;
+    extern __shared__ __align__(16) double sm[];
+    double* As = sm;                 // [128][LDA]
+    double* Bs = sm + GM_ROWS * LDA; // [K][68]
+    double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int r0 = i0 + blockIdx.y * GM_ROWS, cc0 = c0 + blockIdx.x * GM_COLS;
+    // ---- stage A (rows r0.., K columns at kk0) and B (K rows at kk0, 64 columns at cc0): 16-byte cp.async
+    constexpr int ACH = K / 2; // 16-byte chunks per A row
+    for (int e = tid; e < GM_ROWS * ACH; e += 256) {
+        const int r = e / ACH, ch = e - r * ACH;
+        double* dst = As + r * LDA + 2 * ch;
+        if (r0 + r < Np) cp_async16(dst, A + (size_t)(r0 + r) * ld + kk0 + 2 * ch);
+        else { dst[0] = 0.; dst[1] = 0.; }
     }
-    for (int e = tid; e < GT * RT_NB; e += 256) {
-        const int q = e >> 6, c = e & 63;
-        Bs[q][c] = (j0 + c < Np) ? A[(size_t)(k0 + q) * Np + j0 + c] : 0.;
+    for (int e = tid; e < K * (GM_COLS / 2); e += 256) {
+        const int q = e >> 5, ch = e & 31;
+        double* dst = Bs + q * GM_LDB + 2 * ch;
+        if (cc0 + 2 * ch < c1) cp_async16(dst, A + (size_t)(kk0 + q) * ld + cc0 + 2 * ch);
+        else { dst[0] = 0.; dst[1] = 0.; }
     }
-    __syncthreads();
-    const int tx = tid & 15, ty = tid >> 4; // thread tile: rows ty*4.., cols tx*4..
-    double acc[4][4];
+    asm volatile("cp.async.commit_group;");
+    // ---- accumulators <- C
+    const int wr = warp >> 1, wc = warp & 1;
+    const int rw = r0 + wr * 32, cw = cc0 + wc * 32;
+    const int fr = lane >> 2, fc = (lane & 3) * 2;
+    double acc[4][4][2];
 #pragma unroll
-    for (int i = 0; i < 4; i++)
+    for (int ti = 0; ti < 4; ti++)
 #pragma unroll
-        for (int j = 0; j < 4; j++) acc[i][j] = 0.;
-#pragma unroll 8
-    for (int q = 0; q < RT_NB; q++) {
-        double av[4], bv[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) av[i] = As[q][ty * 4 + i];
-#pragma unroll
-        for (int j = 0; j < 4; j++) bv[j] = Bs[q][tx * 4 + j];
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-#pragma unroll
-            for (int j = 0; j < 4; j++) acc[i][j] += av[i] * bv[j];
-    }
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const int r = i0 + ty * 4 + i;
-        if (r < Np) {
-            double* row = A + (size_t)r * Np + j0 + tx * 4;
-            if (j0 + tx * 4 + 3 < Np) {
-                double2 v0 = *reinterpret_cast<double2*>(row), v1 = *reinterpret_cast<double2*>(row + 2);
-                v0.x -= acc[i][0]; v0.y -= acc[i][1]; v1.x -= acc[i][2]; v1.y -= acc[i][3];
-                *reinterpret_cast<double2*>(row) = v0;
-                *reinterpret_cast<double2*>(row + 2) = v1;
+        for (int tj = 0; tj < 4; tj++) {
+            const int r = rw + ti * 8 + fr, c = cw + tj * 8 + fc;
+            if (r < Np && c < c1) {
+                const double2 v = *reinterpret_cast<const double2*>(A + (size_t)r * ld + c);
+                acc[ti][tj][0] = v.x; acc[ti][tj][1] = v.y;
             }
+            else acc[ti][tj][0] = acc[ti][tj][1] = 0.;
         }
+    asm volatile("cp.async.wait_group 0;");
+    __syncthreads();
+    const double* Aw = As + (wr * 32 + fr) * LDA + (lane & 3);
+    const double* Bw = Bs + (lane & 3) * GM_LDB + wc * 32 + fr;
+#pragma unroll 4
+    for (int k4 = 0; k4 < K / 4; k4++) {
+        double af[4], bf[4];
+#pragma unroll
+        for (int ti = 0; ti < 4; ti++) af[ti] = -Aw[ti * 8 * LDA + k4 * 4];
+#pragma unroll
+        for (int tj = 0; tj < 4; tj++) bf[tj] = Bw[k4 * 4 * GM_LDB + tj * 8];
+#pragma unroll
+        for (int ti = 0; ti < 4; ti++)
+#pragma unroll
+            for (int tj = 0; tj < 4; tj++) dmma884(acc[ti][tj][0], acc[ti][tj][1], af[ti], bf[tj]);
     }
+#pragma unroll
+    for (int ti = 0; ti < 4; ti++)
+#pragma unroll
+        for (int tj = 0; tj < 4; tj++) {
+            const int r = rw + ti * 8 + fr, c = cw + tj * 8 + fc;
+            if (r < Np && c < c1) *reinterpret_cast<double2*>(A + (size_t)r * ld + c) = make_double2(acc[ti][tj][0], acc[ti][tj][1]);
+        }
 }
 
-// U x = y, blocked from the bottom; one CTA per layer.  x overwrites rhs.
-__global__ void __launch_bounds__(256) k_backsolve(DevModel d, int nlay_bound)
+// ------------------------------------------------------------------------------------------------------------
+// U x = y (y = column Np after the elimination), blocked from the bottom; one CTA per layer.  x -> d.rhs [L][Np].
+// ------------------------------------------------------------------------------------------------------------
+#define BS_THREADS 512
+__global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int nlay_bound)
 {
     const int a = blockIdx.x;
     if (a >= nlay_bound || a >= *d.n_active) return;
     const int lay = d.active[a];
-    const int Np = d.Np, nb = Np / RT_NB;
-    extern __shared__ double xs[]; // [Np]
+    const int Np = d.Np, ld = d.ld, nb = Np / RT_NB;
+    extern __shared__ double ys[]; // [Np]: y, progressively reduced to y - U[:, done] x[done]
     __shared__ double Us[32][33];
-    __shared__ double ss[32];
-    const double* __restrict__ A = d.Mmat + (size_t)lay * Np * Np;
-    double* __restrict__ b = d.rhs + (size_t)lay * Np;
+    __shared__ double xb[32];
+    const double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
+    double* __restrict__ xo = d.rhs + (size_t)lay * Np;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int r = tid; r < Np; r += BS_THREADS) ys[r] = A[(size_t)r * ld + Np];
     for (int kb = nb - 1; kb >= 0; kb--) {
         const int r0 = kb * RT_NB;
-        // s[r] = y[r] - sum_{c >= r0+32} U[r][c] x[c]
-        for (int rr = warp; rr < 32; rr += 8) {
-            const double* row = A + (size_t)(r0 + rr) * Np;
-            double s = 0.;
-            for (int c = r0 + RT_NB + lane; c < Np; c += 32) s += row[c] * xs[c];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0) ss[rr] = b[r0 + rr] - s;
-            Us[rr][lane] = row[r0 + lane];
-        }
+        for (int rr = warp; rr < 32; rr += BS_THREADS / 32) Us[rr][lane] = A[(size_t)(r0 + rr) * ld + r0 + lane];
         __syncthreads();
         if (warp == 0) {
-            double s = ss[lane];
+            // 32 x 32 upper-triangular solve: x_c = s_c / U_cc, then s_r -= U_rc x_c for r < c
+            double s = ys[r0 + lane];
+            const double diag = Us[lane][lane];
             double xv = 0.;
             for (int c = 31; c >= 0; c--) {
-                const double sc = __shfl_sync(0xffffffffu, s, c);
-                const double xc = sc / Us[c][c];
+                const double xc = __shfl_sync(0xffffffffu, s, c) / __shfl_sync(0xffffffffu, diag, c);
                 if (lane == c) xv = xc;
                 if (lane < c) s -= Us[lane][c] * xc;
             }
-            xs[r0 + lane] = xv;
-            b[r0 + lane] = xv;
+            xb[lane] = xv;
+            xo[r0 + lane] = xv;
         }
         __syncthreads();
+        // right-looking update of everything above: ys[r] -= U[r][r0..r0+31] . x_blk, one warp per row
+        const double xl = xb[lane];
+        int r = warp;
+        for (; r + 3 * (BS_THREADS / 32) < r0; r += 4 * (BS_THREADS / 32)) {
+            double v0 = A[(size_t)r * ld + r0 + lane] * xl;
+            double v1 = A[(size_t)(r + BS_THREADS / 32) * ld + r0 + lane] * xl;
+            double v2 = A[(size_t)(r + 2 * (BS_THREADS / 32)) * ld + r0 + lane] * xl;
+            double v3 = A[(size_t)(r + 3 * (BS_THREADS / 32)) * ld + r0 + lane] * xl;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                v0 += __shfl_xor_sync(0xffffffffu, v0, o); v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+                v2 += __shfl_xor_sync(0xffffffffu, v2, o); v3 += __shfl_xor_sync(0xffffffffu, v3, o);
+            }
+            if (lane == 0) {
+                ys[r] -= v0; ys[r + BS_THREADS / 32] -= v1; ys[r + 2 * (BS_THREADS / 32)] -= v2; ys[r + 3 * (BS_THREADS / 32)] -= v3;
+            }
+        }
+        for (; r < r0; r += BS_THREADS / 32) {
+            double v0 = A[(size_t)r * ld + r0 + lane] * xl;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+            if (lane == 0) ys[r] -= v0;
+        }
+        // the next iteration's barrier after the Us load orders these ys updates before warp 0 reads them
     }
 }
 
-void launch_lu_solve(rt_model* m, cudaStream_t s, int nlay_bound)
+// ------------------------------------------------------------------------------------------------------------
+// host driver
+// ------------------------------------------------------------------------------------------------------------
+static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, int bound)
+{
+    const int m = d.Np - k0;
+    g_rt_launches++;
+    const size_t smem = (size_t)m * 33 * sizeof(double);
+    if (m <= 256) k_panel<1, 256><<<bound, 256, smem, s>>>(d, k0, nleft, bound);
+    else if (m <= 512) k_panel<2, 256><<<bound, 256, smem, s>>>(d, k0, nleft, bound);
+    else k_panel<PNL_BIG_R, PNL_BIG_NT><<<bound, PNL_BIG_NT, smem, s>>>(d, k0, nleft, bound);
+}
+
+static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk0, int c0, int c1, int bound)
+{
+    const dim3 grid((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + GM_ROWS - 1) / GM_ROWS, bound);
+    g_rt_launches++;
+    if (K == 32) k_gemm<32><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
+    else k_gemm<64><<<grid, 256, (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
+}
+
+void launch_lu_solve(rt_model* m, cudaStream_t s, int bound)
 {
     const DevModel& d = m->d;
-    const int Np = d.Np, nb = Np / RT_NB;
-    const int c_panel = rt_prof_class(m, "lu_panel"); 
-    const int c_trsm = rt_prof_class(m, "lu_trsm");
+    const int Np = d.Np, ld = d.ld;
+    const int c_panel = rt_prof_class(m, "lu_panel"), c_trsm = rt_prof_class(m, "lu_trsm");
     const int c_gemm = rt_prof_class(m, "lu_gemm"), c_back = rt_prof_class(m, "lu_backsolve");
-    for (int k = 0; k < nb; k++) {
-        const int mrows = Np - k * RT_NB;
-        const int mt = mrows - RT_NB;
-        const size_t smem = (size_t)mrows * PNL_LD * sizeof(double);
-        rt_prof_begin(m, c_panel, s, 32. * 32. * mrows, 16. * 32. * mrows);
-        g_rt_launches++;
-        k_panel<<<nlay_bound, PNL_THREADS, smem, s>>>(d, k, nlay_bound);
+    auto panel = [&](int k0, int nleft) {
+        const double mr = Np - k0;
+        rt_prof_begin(m, c_panel, s, 32. * 32. * mr, 16. * 32. * mr);
+        launch_panel(d, s, k0, nleft, bound);
         rt_prof_end(m, c_panel, s);
-        if (mt > 0) {
-            rt_prof_begin(m, c_trsm, s, 32. * 32. * mt, 16. * 32. * mt);
-            g_rt_launches++;
-            k_trsm<<<dim3((mt + TRSM_THREADS - 1) / TRSM_THREADS, nlay_bound), TRSM_THREADS, 0, s>>>(d, k, nlay_bound);
-            rt_prof_end(m, c_trsm, s);
-            const int nt = (mt + GT - 1) / GT;
-            rt_prof_begin(m, c_gemm, s, 2. * 32. * mt * mt, 16. * (double)mt * mt);
-            g_rt_launches++;
-            k_gemm<<<dim3(nt, nt, nlay_bound), 256, 0, s>>>(d, k, nlay_bound);
-            rt_prof_end(m, c_gemm, s);
+    };
+    auto trsm = [&](int k0, int mode) {
+        const int c0 = k0 + 32;
+        const double nc = ld - c0;
+        rt_prof_begin(m, c_trsm, s, (mode == 2 ? 3. : 1.) * 32. * 32. * nc, (mode == 2 ? 24. : 16.) * 32. * nc);
+        g_rt_launches++;
+        k_trsm<<<dim3((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, bound), TRSM_THREADS, 0, s>>>(d, k0, c0, mode, bound);
+        rt_prof_end(m, c_trsm, s);
+    };
+    auto gemm = [&](int K, int i0, int kk0, int c0, int c1) {
+        const double mr = Np - i0, nc = c1 - c0;
+        rt_prof_begin(m, c_gemm, s, 2. * K * mr * nc, 16. * mr * nc + 8. * K * (mr + nc));
+        launch_gemm(d, s, K, i0, kk0, c0, c1, bound);
+        rt_prof_end(m, c_gemm, s);
+    };
+    for (int k0 = 0; k0 < Np; k0 += 64) {
+        panel(k0, 0);
+        trsm(k0, 1);
+        if (k0 + 32 < Np) {
+            gemm(32, k0 + 32, k0, k0 + 32, k0 + 64);
+            panel(k0 + 32, 32);
+            trsm(k0 + 32, 2);
+            if (k0 + 64 < Np) gemm(64, k0 + 64, k0, k0 + 64, ld);
         }
     }
     rt_prof_begin(m, c_back, s, (double)Np * Np, 4. * Np * Np);
     g_rt_launches++;
-    k_backsolve<<<nlay_bound, 256, Np * sizeof(double), s>>>(d, nlay_bound);
+    k_backsolve<<<bound, BS_THREADS, Np * sizeof(double), s>>>(d, bound);
     rt_prof_end(m, c_back, s);
 }
 
-// dynamic shared memory opt-in (up to 227 KB per CTA on sm_100)
-int lu_max_np() { return LU_PANEL_SMEM_MAX / (PNL_LD * (int)sizeof(double)) / RT_NB * RT_NB; }
+int lu_max_np() { return PNL_MAXROWS; }
 
 cudaError_t lu_kernels_init()
 {
-    return cudaFuncSetAttribute(k_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, LU_PANEL_SMEM_MAX);
+    cudaError_t e = cudaFuncSetAttribute(k_panel<1, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 33 * (int)sizeof(double));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_panel<2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 512 * 33 * (int)sizeof(double));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_panel<PNL_BIG_R, PNL_BIG_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 768 * 33 * (int)sizeof(double));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_gemm<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_gemm<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 36 + 32 * GM_LDB) * (int)sizeof(double));
 }

@@ -153,7 +153,7 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
     const int K = desc->nb_neutral_tables + desc->nb_electron_tables;
     if (N < 2 || !desc->energy || !desc->g || !desc->einst || K > RT_MAX_TABLES || desc->dust_ncomp > RT_MAX_DUST
         || desc->dust_ncomp < 1 || !desc->lvg.p) { g_create_error = "inconsistent rt_model_desc"; return RT_ERR_INVALID; }
-    if ((N + RT_NB - 1) / RT_NB * RT_NB > lu_max_np()) { g_create_error = "nb_lev too large for the shared-memory LU panel (max 864)"; return RT_ERR_UNSUPPORTED; }
+    if ((N + RT_NB - 1) / RT_NB * RT_NB > lu_max_np()) { g_create_error = "nb_lev too large for the register-resident LU panel (max 768, the reference's largest molecule)"; return RT_ERR_UNSUPPORTED; }
     if (desc->params.nb_prev_steps != 5) { g_create_error = "only nb_prev_steps == 5 is implemented"; return RT_ERR_UNSUPPORTED; }
     if (desc->scheme == RT_SCHEME_LINE_OVERLAP && (!desc->overlap1 || !desc->overlap2)) { g_create_error = "overlap tables missing"; return RT_ERR_INVALID; }
     if ((desc->species_rule == RT_RULE_CH3OH || desc->species_rule == RT_RULE_OH_HF) && desc->nb_neutral_tables < 3) { g_create_error = "rule needs 3 neutral tables"; return RT_ERR_INVALID; }
@@ -178,6 +178,7 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
     DevModel& d = m->d;
     d.N = N;
     d.Np = (N + RT_NB - 1) / RT_NB * RT_NB;
+    d.ld = d.Np + RT_NB;
     d.K = K; d.nb1 = desc->nb_neutral_tables; d.nb2 = K;
     d.rule = desc->species_rule; d.scheme = desc->scheme; d.ncomp = desc->dust_ncomp;
     d.prm = desc->params; d.mol_mass = desc->mol_mass;
@@ -444,7 +445,7 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
 
     const size_t mat = (size_t)L * Np * Np;
     d.Cmat = dev_alloc<double>(m, mat, true, false);
-    d.Mmat = dev_alloc<double>(m, mat, true, false);
+    d.Mmat = dev_alloc<double>(m, (size_t)L * Np * d.ld, true, false);
     d.pop = dev_alloc<double>(m, (size_t)L * N, true);
     d.rhs = dev_alloc<double>(m, (size_t)L * Np, true);
     d.hist_pop = dev_alloc<double>(m, (size_t)L * RT_HIST * N, true);
@@ -453,6 +454,7 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
     d.yd = dev_alloc<double>(m, (size_t)L * std::max(1, d.R), true);
     d.yu = dev_alloc<double>(m, (size_t)L * std::max(1, d.R), true);
     d.ipiv = dev_alloc<int>(m, (size_t)L * Np, true);
+    d.lu_aff = dev_alloc<int>(m, (size_t)L * (Np / RT_NB) * RT_AFF_STRIDE, true);
     int** ip[] = {&d.iter_nb, &d.nb_after, &d.head_pop, &d.head_res, &d.n_hist_pop, &d.n_hist_res, &d.conv, &d.active_flag, &d.active};
     for (int** p : ip) *p = dev_alloc<int>(m, L, true);
     double** dp[] = {&d.best_eq, &d.eq_err, &d.pop_err, &d.rel_err};
@@ -713,7 +715,7 @@ rt_status rt_assemble(rt_model* m, const double* pop, double* matrix, double* df
     cudaFree(df_dev);
     if (matrix) // strip the padding, layer by layer
         for (int l = 0; l < L; l++)
-            CK(cudaMemcpy2D(matrix + (size_t)l * N * N, sizeof(double) * N, d.Mmat + (size_t)l * Np * Np, sizeof(double) * Np,
+            CK(cudaMemcpy2D(matrix + (size_t)l * N * N, sizeof(double) * N, d.Mmat + (size_t)l * Np * d.ld, sizeof(double) * d.ld,
                             sizeof(double) * N, N, cudaMemcpyDeviceToHost));
     return RT_OK;
 }

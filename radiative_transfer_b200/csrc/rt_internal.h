@@ -4,11 +4,13 @@
 //   Cmat [L][Np][Np]  collisional part of the rate matrix of every layer, in the layout of the reference's
 //                     `matrix` (iteration_lvg.cpp:127-131): entry [j][i] = rate i->j, diagonal = -(column sum).
 //                     Built ONCE per cloud (it depends on the layer only).
-//   Mmat [L][Np][Np]  per-iteration rate matrix = Cmat + radiative terms, row 0 = 1; destroyed by the LU.
+//   Mmat [L][Np][ld]  per-iteration rate matrix = Cmat + radiative terms, row 0 = 1; destroyed by the LU.
+//                     ld = Np + 32: column Np carries the right-hand side e0 through the elimination (so the
+//                     forward substitution is part of the blocked update), columns Np+1.. are zero padding.
 //   Np = N rounded up to a multiple of 32; the padding is an identity block so that every blocked kernel works
 //   on whole 32x32 tiles without edge cases (padded unknowns solve to 0 and never couple to real levels).
 //   pop  [L][N]       current populations (pop_old of iteration_control::next_step)
-//   rhs  [L][Np]      right-hand side e0 -> solution (new populations)
+//   rhs  [L][Np]      solution of M x = e0 (new populations), written by the back substitution
 //   hist_pop/hist_res [L][6][N]  rings of the last nb_prev_steps+1 population / residual vectors
 #pragma once
 #include <cuda_runtime.h>
@@ -21,6 +23,7 @@
 #define RT_MAX_TABLES 16
 #define RT_MAX_DUST 8
 #define RT_NB 32 // LU panel width == padding granularity
+#define RT_AFF_STRIDE 132 // {n_aff, pad, pad, pad, pos[64], cur[64]}
 
 struct DevTable {            // one collision_data, transposed to [jmax][imax] so one layer's T-row is contiguous
     int nb_lev, jmax, imax, pad;
@@ -35,7 +38,7 @@ struct DevOverlap { int nb_d, nb_dx, nb_gr, nb_g; const double *log_delta, *dx, 
 
 // Everything a kernel needs, passed by value (fits the 4 KB parameter space).
 struct DevModel {
-    int N, Np, R, G, L, ncomp, K, nb1, nb2, rule, scheme, pad0;
+    int N, Np, R, G, L, ncomp, K, nb1, nb2, rule, scheme, ld; // ld = Np + 32: row stride of Mmat (rhs rides as column Np)
     rt_params prm;
     double mol_mass;
     // levels
@@ -59,6 +62,7 @@ struct DevModel {
     // big per-layer state
     double *Cmat, *Mmat, *pop, *rhs, *hist_pop, *hist_res, *opt, *yd, *yu;
     int* ipiv;               // [L][Np]
+    int* lu_aff;             // [L][Np/32][RT_AFF_STRIDE] row permutation of every panel (see lu_kernels.cu)
     // controller state [L]
     int *iter_nb, *nb_after, *head_pop, *head_res, *n_hist_pop, *n_hist_res, *conv, *active_flag;
     double *best_eq, *eq_err, *pop_err, *rel_err;
