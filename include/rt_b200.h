@@ -109,6 +109,8 @@ typedef struct rt_overlap_table {
     const double* gratio; /* [nb_gr] */
     const double* gamma;  /* [nb_g]  */
     const double* p;      /* [nb_d*nb_dx][nb_gr*nb_g] */
+    int delta_is_log10;   /* != 0: delta[] already holds log10(delta), as lvg_line_overlap_data keeps it in memory */
+    int reserved0;
 } rt_overlap_table;
 
 /* Molecule + physics tables: replaces energy_diagram (spectroscopy.h:69-87), einstein_coeff (:179-190),

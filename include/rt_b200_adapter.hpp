@@ -1,0 +1,245 @@
+// rt_b200_adapter.hpp -- header-only C++ adapter between the REFERENCE's own classes and the C ABI of librt_b200.so.
+//
+// A maintainer of nesterenok/radiative_transfer adds this header to the driver and replaces the call
+//     calc_molecular_populations(cloud, it_scheme, levels, einst, coll, popul, nb_lev, accel, verbosity)
+// (radiative_transfer.cpp:219, call sites :440,571,670,797,925,1058,...) by
+//     rt_b200::calc_molecular_populations_gpu(cloud, it_scheme, levels, einst, coll, popul, nb_lev, accel, verbosity)
+// -- same arguments, same in/out array `popul[lay*nb_lev + lev]`, same stdout report of bad layers.
+// Everything is read from the reference's objects (no text files are re-parsed): protected members are reached
+// through derived accessor classes (pointer-to-member of a protected base member, legal C++).
+// Compiles only inside the reference's tree (it includes the reference's headers); nothing here is used by the
+// Python host side.  Exercised by oracle/ref_harness.cpp (ref_adapter_*), tests/test_adapter.py.
+#pragma once
+#include <cmath>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "cloud_data.h"
+#include "coll_rates.h"
+#include "coll_rates_ch3oh.h"
+#include "coll_rates_h2o.h"
+#include "coll_rates_oh.h"
+#include "dust_model.h"
+#include "iteration_lvg.h"
+#include "lvg_method_functions.h"
+#include "spectroscopy.h"
+
+#include "rt_b200.h"
+
+namespace rt_b200 {
+
+// ---- accessors to protected members of the reference's classes ------------------------------------------------
+struct coll_access : public collisional_transitions {
+    static const std::vector<collision_data*>& data(const collisional_transitions* c) { return c->*(&coll_access::coll_data); }
+    static int n1(const collisional_transitions* c) { return c->*(&coll_access::nb1); }
+    static int n2(const collisional_transitions* c) { return c->*(&coll_access::nb2); }
+};
+struct lvg_access : public lvg_method_data {
+    static int nd(const lvg_method_data* t) { return t->*(&lvg_access::nb_d); }
+    static int ng(const lvg_method_data* t) { return t->*(&lvg_access::nb_g); }
+    static const double* delta(const lvg_method_data* t) { return t->*(&lvg_access::delta_arr); }
+    static const double* gamma(const lvg_method_data* t) { return t->*(&lvg_access::gamma_arr); }
+    static double** p(const lvg_method_data* t) { return t->*(&lvg_access::p_arr); }
+};
+struct ovl_access : public lvg_line_overlap_data {
+    static int nd(const lvg_line_overlap_data* t) { return t->*(&ovl_access::nb_d); }
+    static int ng(const lvg_line_overlap_data* t) { return t->*(&ovl_access::nb_g); }
+    static int ngr(const lvg_line_overlap_data* t) { return t->*(&ovl_access::nb_gr); }
+    static int ndx(const lvg_line_overlap_data* t) { return t->*(&ovl_access::nb_dx); }
+    static const double* delta(const lvg_line_overlap_data* t) { return t->*(&ovl_access::delta_arr); } // log10 (cpp:293)
+    static const double* gamma(const lvg_line_overlap_data* t) { return t->*(&ovl_access::gamma_arr); }
+    static const double* gratio(const lvg_line_overlap_data* t) { return t->*(&ovl_access::gratio_arr); }
+    static const double* dx(const lvg_line_overlap_data* t) { return t->*(&ovl_access::dx_arr); }
+    static double** p(const lvg_line_overlap_data* t) { return t->*(&ovl_access::p_arr); }
+};
+struct dustc_access : public dust_component {
+    static int n(const dust_component* c) { return c->*(&dustc_access::nb_ph_en); }
+    static const double* en(const dust_component* c) { return c->*(&dustc_access::ph_en_arr); }
+    static const double* abs(const dust_component* c) { return c->*(&dustc_access::abs_coeff); }
+};
+struct scheme_access : public iteration_scheme_lvg {
+    static const dust_model* dust_of(const iteration_scheme_lvg* s) { return s->*(&scheme_access::dust); }
+    static const lvg_method_data* lvg_of(const iteration_scheme_lvg* s) { return s->*(&scheme_access::loss_func_line_phot); }
+};
+struct overlap_access : public iteration_scheme_line_overlap {
+    static const std::vector<hfs_lines>& groups(const iteration_scheme_line_overlap* s) { return s->*(&overlap_access::line_list); }
+    static const lvg_line_overlap_data* t1(const iteration_scheme_line_overlap* s) { return s->*(&overlap_access::line_overlap1); }
+    static const lvg_line_overlap_data* t2(const iteration_scheme_line_overlap* s) { return s->*(&overlap_access::line_overlap2); }
+    static double maxdx(const iteration_scheme_line_overlap* s) { return s->*(&overlap_access::max_dx); }
+};
+
+// the species mixing rule implemented by the dynamic type of `coll` (coll_rates_ch3oh.cpp:484, coll_rates_oh.cpp:392,
+// coll_rates_h2o.cpp:530); anything else follows the base-class rule coll_rates.cpp:181-197
+inline int species_rule_of(const collisional_transitions* coll)
+{
+    if (dynamic_cast<const ch3oh_collisions*>(coll)) return RT_RULE_CH3OH;
+    if (dynamic_cast<const oh_hf_collisions*>(coll)) return RT_RULE_OH_HF;
+    if (dynamic_cast<const h2o_collisions*>(coll)) return RT_RULE_H2O;
+    return RT_RULE_GENERIC;
+}
+
+// ---- flattened copies (own the storage the rt_*_desc structs point into) ------------------------------------------
+struct flat_model {
+    std::vector<double> energy, j, einst, lvg_delta, lvg_gamma, lvg_p;
+    std::vector<int> g, v, groups;
+    std::vector<std::vector<double>> tgrid, coeff, dust_en, dust_abs;
+    std::vector<rt_coll_table> tables;
+    std::vector<rt_dust_comp> dust;
+    std::vector<double> ov_p[2];
+    rt_overlap_table ov[2];
+    std::string name;
+    rt_model_desc desc;
+};
+
+inline void flatten_overlap(const lvg_line_overlap_data* t, std::vector<double>& p, rt_overlap_table& o)
+{
+    o.nb_d = ovl_access::nd(t); o.nb_dx = ovl_access::ndx(t); o.nb_gr = ovl_access::ngr(t); o.nb_g = ovl_access::ng(t);
+    o.delta = ovl_access::delta(t); o.delta_is_log10 = 1; // the reference stores log10(delta), lvg_method_functions.cpp:293
+    o.dx = ovl_access::dx(t); o.gratio = ovl_access::gratio(t); o.gamma = ovl_access::gamma(t);
+    const size_t rows = (size_t)o.nb_d * o.nb_dx, cols = (size_t)o.nb_gr * o.nb_g;
+    p.resize(rows * cols);
+    for (size_t r = 0; r < rows; r++) memcpy(&p[r * cols], ovl_access::p(t)[r], sizeof(double) * cols);
+    o.p = p.data();
+    o.reserved0 = 0;
+}
+
+// Reads energy_diagram / einstein_coeff / collisional_transitions and, through the scheme, the dust model and the
+// escape-probability tables (for iteration_scheme_line_overlap also the reference's own line_list and max_dx).
+inline void flatten_model(const iteration_scheme_lvg* scheme, const energy_diagram* levels, const einstein_coeff* einst,
+                          const collisional_transitions* coll, int species_rule, flat_model& f)
+{
+    const int N = levels->nb_lev;
+    rt_model_desc& d = f.desc;
+    memset(&d, 0, sizeof d);
+    rt_params_default(&d.params);
+    f.energy.resize(N); f.j.resize(N); f.g.resize(N); f.v.resize(N);
+    for (int i = 0; i < N; i++) {
+        const energy_level& l = levels->lev_array[i];
+        f.energy[i] = l.energy; f.g[i] = l.g; f.v[i] = l.v; f.j[i] = l.j;
+    }
+    f.einst.resize((size_t)N * N);
+    for (int i = 0; i < N; i++) memcpy(&f.einst[(size_t)i * N], einst->arr[i], sizeof(double) * N);
+    f.name = levels->mol.name;
+    d.nb_lev = N; d.species_rule = species_rule < 0 ? species_rule_of(coll) : species_rule;
+    d.energy = f.energy.data(); d.g = f.g.data(); d.v = f.v.data(); d.j = f.j.data();
+    d.mol_mass = levels->mol.mass; d.mol_name = f.name.c_str(); d.einst = f.einst.data();
+
+    const std::vector<collision_data*>& cd = coll_access::data(coll);
+    const int nb1 = coll_access::n1(coll), nb2 = coll_access::n2(coll); // tables [nb2, nb3) are ion data: not used by the scheme
+    f.tables.resize(nb2); f.tgrid.resize(nb2); f.coeff.resize(nb2);
+    for (int k = 0; k < nb2; k++) {
+        const collision_data* t = cd[k];
+        f.tgrid[k].assign(t->tgrid, t->tgrid + t->jmax);
+        f.coeff[k].resize((size_t)t->imax * t->jmax);
+        for (int i = 0; i < t->imax; i++) memcpy(&f.coeff[k][(size_t)i * t->jmax], t->coeff[i], sizeof(double) * t->jmax);
+        f.tables[k].nb_lev = t->nb_lev; f.tables[k].jmax = t->jmax;
+        f.tables[k].tgrid = f.tgrid[k].data(); f.tables[k].coeff = f.coeff[k].data();
+    }
+    d.nb_neutral_tables = nb1; d.nb_electron_tables = nb2 - nb1; d.tables = f.tables.data();
+
+    const lvg_method_data* lt = scheme_access::lvg_of(scheme);
+    const int nd = lvg_access::nd(lt), ng = lvg_access::ng(lt);
+    f.lvg_delta.assign(lvg_access::delta(lt), lvg_access::delta(lt) + nd);
+    f.lvg_gamma.assign(lvg_access::gamma(lt), lvg_access::gamma(lt) + ng);
+    f.lvg_p.resize((size_t)nd * ng);
+    for (int i = 0; i < nd; i++) memcpy(&f.lvg_p[(size_t)i * ng], lvg_access::p(lt)[i], sizeof(double) * ng);
+    d.lvg.nb_d = nd; d.lvg.nb_g = ng; d.lvg.delta = f.lvg_delta.data(); d.lvg.gamma = f.lvg_gamma.data(); d.lvg.p = f.lvg_p.data();
+
+    d.scheme = RT_SCHEME_LVG;
+    if (const iteration_scheme_line_overlap* so = dynamic_cast<const iteration_scheme_line_overlap*>(scheme)) {
+        d.scheme = RT_SCHEME_LINE_OVERLAP;
+        d.params.max_dx = overlap_access::maxdx(so);
+        for (const hfs_lines& h : overlap_access::groups(so)) { // the reference's own grouping, iteration_lvg.cpp:317-346
+            const int g5[5] = {h.nb, h.upl[0], h.lowl[0], h.nb > 1 ? h.upl[1] : -1, h.nb > 1 ? h.lowl[1] : -1};
+            f.groups.insert(f.groups.end(), g5, g5 + 5);
+        }
+        d.nb_line_groups = (int)f.groups.size() / 5; d.line_groups = f.groups.data();
+        flatten_overlap(overlap_access::t1(so), f.ov_p[0], f.ov[0]);
+        flatten_overlap(overlap_access::t2(so), f.ov_p[1], f.ov[1]);
+        d.overlap1 = &f.ov[0]; d.overlap2 = &f.ov[1];
+    }
+
+    const dust_model* dm = scheme_access::dust_of(scheme);
+    f.dust.resize(dm->nb_of_comp); f.dust_en.resize(dm->nb_of_comp); f.dust_abs.resize(dm->nb_of_comp);
+    for (int c = 0; c < dm->nb_of_comp; c++) {
+        const dust_component* dc = dm->components[c];
+        const int n = dustc_access::n(dc);
+        f.dust_en[c].assign(dustc_access::en(dc), dustc_access::en(dc) + n);
+        f.dust_abs[c].assign(dustc_access::abs(dc), dustc_access::abs(dc) + n);
+        f.dust[c].nb_ph_en = n; f.dust[c].reserved0 = 0; f.dust[c].ph_en = f.dust_en[c].data();
+        f.dust[c].abs_coeff = f.dust_abs[c].data(); f.dust[c].wvl_exp = dc->wvl_exp;
+    }
+    d.dust_ncomp = dm->nb_of_comp; d.dust = f.dust.data();
+}
+
+struct flat_cloud {
+    std::vector<double> a[12], dust_conc;
+    rt_layer_soa soa;
+};
+
+// cloud_data / cloud_layer (cloud_data.h:24-78) -> layer-major SoA
+inline void flatten_cloud(const cloud_data* cloud, flat_cloud& f)
+{
+    const int L = cloud->nb_lay;
+    const int nc = L > 0 ? (int)cloud->lay_array[0].dust_grain_conc.size() : 0;
+    for (auto& v : f.a) v.resize(L);
+    f.dust_conc.resize((size_t)L * nc);
+    for (int l = 0; l < L; l++) {
+        const cloud_layer& c = cloud->lay_array[l];
+        const double v[12] = {c.temp_n, c.temp_el, c.el_conc, c.h_conc, c.ph2_conc, c.oh2_conc, c.he_conc, c.mol_conc,
+                              c.vel_turb, c.velg_n, c.dz, c.vel_n};
+        for (int k = 0; k < 12; k++) f.a[k][l] = v[k];
+        for (int k = 0; k < nc; k++) f.dust_conc[(size_t)l * nc + k] = k < (int)c.dust_grain_conc.size() ? c.dust_grain_conc[k] : 0.;
+    }
+    rt_layer_soa& s = f.soa;
+    memset(&s, 0, sizeof s);
+    s.nb_lay = L; s.dust_ncomp = nc;
+    s.temp_n = f.a[0].data(); s.temp_el = f.a[1].data(); s.el_conc = f.a[2].data(); s.h_conc = f.a[3].data();
+    s.ph2_conc = f.a[4].data(); s.oh2_conc = f.a[5].data(); s.he_conc = f.a[6].data(); s.mol_conc = f.a[7].data();
+    s.vel_turb = f.a[8].data(); s.velg_n = f.a[9].data(); s.dz = f.a[10].data(); s.vel_n = f.a[11].data();
+    s.dust_conc = f.dust_conc.data();
+    s.height = cloud->get_height();
+}
+
+// Drop-in for calc_molecular_populations (radiative_transfer.cpp:219-289).  start_mode RT_START_CHAINED reproduces the
+// reference's warm-start chain exactly (serial over layers); the default RT_START_BOUNDARY starts every layer from
+// boundary_layer_populations -- the reference's own start for layer 0 and after a failed layer (:250-253) -- and solves
+// all layers at once on the GPU.  Fatal conditions are reported like the reference does (message to cout) but return
+// false instead of exit(1).  max_iter_acc / max_iter_ext / min_err: MAX_NB_ITER_ACC, MAX_NB_ITER_EXT (:26-27),
+// rel_population_error (:45).
+inline bool calc_molecular_populations_gpu(cloud_data* cloud, iteration_scheme_lvg* it_scheme_lvg, energy_diagram* mol_levels,
+                                           einstein_coeff* mol_einst, collisional_transitions* mol_coll, double* mol_popul,
+                                           int nb_lev, bool acceleration, int verbosity, int start_mode = RT_START_BOUNDARY,
+                                           int device = 0, int species_rule = -1, rt_layer_status* status = nullptr,
+                                           int max_iter_acc = 150, int max_iter_ext = 15000, double min_err = 1.e-5)
+{
+    flat_model fm;
+    flat_cloud fc;
+    flatten_model(it_scheme_lvg, mol_levels, mol_einst, mol_coll, species_rule, fm);
+    flatten_cloud(cloud, fc);
+    if (nb_lev != fm.desc.nb_lev) { std::cout << "rt_b200: nb_lev differs from the energy diagram" << std::endl; return false; }
+    rt_model* m = nullptr;
+    rt_status rc = rt_model_create(&fm.desc, device, &m);
+    if (rc != RT_OK) { std::cout << "rt_b200: " << rt_status_string(rc) << ": " << rt_last_error(nullptr) << std::endl; return false; }
+    std::vector<rt_layer_status> st(cloud->nb_lay);
+    rc = rt_cloud_upload(m, &fc.soa);
+    if (rc == RT_OK)
+        rc = rt_calc_molecular_populations(m, mol_popul, start_mode, acceleration ? 1 : 0, max_iter_acc, max_iter_ext, min_err, st.data());
+    if (rc != RT_OK) std::cout << "rt_b200: " << rt_status_string(rc) << ": " << rt_last_error(m) << std::endl;
+    rt_model_destroy(m);
+    if (rc != RT_OK) return false;
+    bool any_bad = false;
+    for (int l = 0; l < cloud->nb_lay; l++) any_bad = any_bad || !st[l].converged;
+    if (verbosity && any_bad) { // radiative_transfer.cpp:283-288
+        std::cout << "Can not find solution for layers:" << std::endl;
+        for (int l = 0; l < cloud->nb_lay; l++)
+            if (!st[l].converged) std::cout << l << " ";
+        std::cout << std::endl;
+    }
+    if (status) memcpy(status, st.data(), sizeof(rt_layer_status) * st.size());
+    return true;
+}
+
+} // namespace rt_b200

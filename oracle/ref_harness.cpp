@@ -676,3 +676,82 @@ int ref_maser_postpass(const rt_model_desc* d, const rt_layer_soa* lay, const do
 }
 
 } // extern "C"
+
+// =========================================================================================================
+// Adapter checks (include/rt_b200_adapter.hpp): built into oracle/_ref/libref_adapter.so, which links librt_b200.so.
+// The reference objects are built from the flat problem as above; the ADAPTER then reads them back (through the
+// reference's own class surface) and drives the CUDA library -- the drop-in path a maintainer would use.
+// =========================================================================================================
+#ifdef RT_WITH_ADAPTER
+#include "../include/rt_b200_adapter.hpp"
+
+extern "C" {
+
+// flatten(reference objects) must reproduce the flat problem the objects were built from: returns the number of
+// mismatching scalars/array elements (0 = byte-identical round trip), -1 on a structural mismatch.
+int ref_adapter_roundtrip(const rt_model_desc* d, const rt_layer_soa* lay)
+{
+    ref_ctx* c = build_ctx(d, lay);
+    rt_b200::flat_model fm;
+    rt_b200::flat_cloud fc;
+    rt_b200::flatten_model(c->scheme, c->diagram, c->einst, c->coll, d->species_rule, fm);
+    rt_b200::flatten_cloud(c->cloud, fc);
+    const rt_model_desc& q = fm.desc;
+    long bad = 0;
+    auto cmp = [&](const double* a, const double* b, size_t n) { for (size_t i = 0; i < n; i++) bad += (a[i] != b[i]); };
+    if (q.nb_lev != d->nb_lev || q.nb_neutral_tables != d->nb_neutral_tables || q.nb_electron_tables != d->nb_electron_tables
+        || q.scheme != d->scheme || q.dust_ncomp != d->dust_ncomp || q.lvg.nb_d != d->lvg.nb_d || q.lvg.nb_g != d->lvg.nb_g
+        || fc.soa.nb_lay != lay->nb_lay || fc.soa.dust_ncomp != lay->dust_ncomp) { delete c; return -1; }
+    const int N = d->nb_lev;
+    cmp(q.energy, d->energy, N); cmp(q.einst, d->einst, (size_t)N * N);
+    for (int i = 0; i < N; i++) bad += (q.g[i] != d->g[i]) + (d->v && q.v[i] != d->v[i]) + (d->j && q.j[i] != d->j[i]);
+    bad += (q.mol_mass != d->mol_mass);
+    for (int k = 0; k < q.nb_neutral_tables + q.nb_electron_tables; k++) {
+        if (q.tables[k].nb_lev != d->tables[k].nb_lev || q.tables[k].jmax != d->tables[k].jmax) { delete c; return -1; }
+        cmp(q.tables[k].tgrid, d->tables[k].tgrid, q.tables[k].jmax);
+        cmp(q.tables[k].coeff, d->tables[k].coeff, (size_t)q.tables[k].jmax * q.tables[k].nb_lev * (q.tables[k].nb_lev - 1) / 2);
+    }
+    cmp(q.lvg.delta, d->lvg.delta, q.lvg.nb_d); cmp(q.lvg.gamma, d->lvg.gamma, q.lvg.nb_g);
+    cmp(q.lvg.p, d->lvg.p, (size_t)q.lvg.nb_d * q.lvg.nb_g);
+    if (d->scheme == RT_SCHEME_LINE_OVERLAP) {
+        const rt_overlap_table* a[2] = {q.overlap1, q.overlap2};
+        const rt_overlap_table* b[2] = {d->overlap1, d->overlap2};
+        for (int t = 0; t < 2; t++) {
+            if (a[t]->nb_d != b[t]->nb_d || a[t]->nb_dx != b[t]->nb_dx || a[t]->nb_gr != b[t]->nb_gr || a[t]->nb_g != b[t]->nb_g) { delete c; return -1; }
+            for (int i = 0; i < a[t]->nb_d; i++) bad += (a[t]->delta[i] != log10(b[t]->delta[i]));
+            cmp(a[t]->dx, b[t]->dx, a[t]->nb_dx); cmp(a[t]->gratio, b[t]->gratio, a[t]->nb_gr); cmp(a[t]->gamma, b[t]->gamma, a[t]->nb_g);
+            cmp(a[t]->p, b[t]->p, (size_t)a[t]->nb_d * a[t]->nb_dx * a[t]->nb_gr * a[t]->nb_g);
+        }
+    }
+    for (int k = 0; k < q.dust_ncomp; k++) {
+        if (q.dust[k].nb_ph_en != d->dust[k].nb_ph_en) { delete c; return -1; }
+        if (c->dust_exact) cmp(q.dust[k].ph_en, d->dust[k].ph_en, q.dust[k].nb_ph_en);
+        cmp(q.dust[k].abs_coeff, d->dust[k].abs_coeff, q.dust[k].nb_ph_en);
+        bad += (q.dust[k].wvl_exp != d->dust[k].wvl_exp);
+    }
+    const double* la[] = {fc.soa.temp_n, fc.soa.temp_el, fc.soa.el_conc, fc.soa.h_conc, fc.soa.ph2_conc, fc.soa.oh2_conc, fc.soa.he_conc,
+                          fc.soa.mol_conc, fc.soa.vel_turb, fc.soa.velg_n, fc.soa.dz, fc.soa.vel_n};
+    const double* lb[] = {lay->temp_n, lay->temp_el, lay->el_conc, lay->h_conc, lay->ph2_conc, lay->oh2_conc, lay->he_conc,
+                          lay->mol_conc, lay->vel_turb, lay->velg_n, lay->dz, lay->vel_n};
+    for (int k = 0; k < 12; k++) cmp(la[k], lb[k], lay->nb_lay);
+    cmp(fc.soa.dust_conc, lay->dust_conc, (size_t)lay->nb_lay * lay->dust_ncomp);
+    bad += (fc.soa.height != lay->height);
+    delete c;
+    return (int)bad;
+}
+
+// reference objects -> adapter -> librt_b200.so (GPU).  Returns 0 on success, 1 if the adapter reported failure.
+int ref_adapter_calc_molecular_populations(const rt_model_desc* d, const rt_layer_soa* lay, double* pop, int acceleration,
+                                           int start_mode, int device, rt_layer_status* st)
+{
+    ref_ctx* c = build_ctx(d, lay);
+    null_buf nb;
+    cout_redirect quiet(&nb);
+    const bool ok = rt_b200::calc_molecular_populations_gpu(c->cloud, c->scheme, c->diagram, c->einst, c->coll, pop, c->N,
+                                                            acceleration != 0, 0, start_mode, device, d->species_rule, st);
+    delete c;
+    return ok ? 0 : 1;
+}
+
+} // extern "C"
+#endif

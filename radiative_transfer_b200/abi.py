@@ -48,7 +48,7 @@ class rt_lvg_table(C.Structure):
 class rt_overlap_table(C.Structure):
     _fields_ = [("nb_d", C.c_int), ("nb_dx", C.c_int), ("nb_gr", C.c_int), ("nb_g", C.c_int),
                 ("delta", c_double_p), ("dx", c_double_p), ("gratio", c_double_p), ("gamma", c_double_p),
-                ("p", c_double_p)]
+                ("p", c_double_p), ("delta_is_log10", C.c_int), ("reserved0", C.c_int)]
 
 
 class rt_model_desc(C.Structure):

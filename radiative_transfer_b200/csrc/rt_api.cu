@@ -294,7 +294,7 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
         for (int q = 0; q < 2; q++) {
             const rt_overlap_table& o = *src[q];
             std::vector<double> ld(o.nb_d);
-            for (int i = 0; i < o.nb_d; i++) ld[i] = log10(o.delta[i]); // lvg_method_functions.cpp:293
+            for (int i = 0; i < o.nb_d; i++) ld[i] = o.delta_is_log10 ? o.delta[i] : log10(o.delta[i]); // lvg_method_functions.cpp:293
             d.ov[q].nb_d = o.nb_d; d.ov[q].nb_dx = o.nb_dx; d.ov[q].nb_gr = o.nb_gr; d.ov[q].nb_g = o.nb_g;
             d.ov[q].log_delta = dev_upload(m, ld.data(), o.nb_d, false);
             d.ov[q].dx = dev_upload(m, o.dx, o.nb_dx, false);
