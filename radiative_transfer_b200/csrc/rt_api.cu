@@ -6,8 +6,12 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 
 cudaError_t lu_kernels_init();
+cudaError_t fused_kernels_init();
+bool fused_supported(const DevModel& d);
+void launch_fused_solve(const DevModel& d, cudaStream_t s, int nlay, int accel, int max_iter, double min_err);
 int lu_max_np();
 void launch_ctl_init_flagged(const DevModel& d, cudaStream_t s, int accel);
 void launch_set_active_range(const DevModel& d, cudaStream_t s, int b, int e);
@@ -171,9 +175,11 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
     if (prop.major < 10) { g_create_error = "librt_b200 is built for sm_100a only"; delete m; return RT_ERR_CUDA; }
     if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess) { g_create_error = "stream"; delete m; return RT_ERR_CUDA; }
     if (cudaMallocHost((void**)&m->h_n_active, 4 * sizeof(int)) != cudaSuccess) { g_create_error = "pinned alloc"; delete m; return RT_ERR_CUDA; }
+    if (cudaError_t ce = fused_kernels_init()) { g_create_error = std::string("cudaFuncSetAttribute failed: ") + cudaGetErrorString(ce); delete m; return RT_ERR_CUDA; }
     if (cudaError_t ce = lu_kernels_init()) { g_create_error = std::string("cudaFuncSetAttribute failed: ") + cudaGetErrorString(ce); delete m; return RT_ERR_CUDA; }
 
     m->desc = *desc;
+    m->use_fused = getenv("RT_B200_NO_FUSED") == nullptr; // development switch: force the multi-kernel path
     m->mol_name = desc->mol_name ? desc->mol_name : "";
     DevModel& d = m->d;
     d.N = N;
@@ -546,6 +552,21 @@ static rt_status solve_range(rt_model* m, int lb, int le, int start_mode, int ma
     m->prof_layers = bound;
     enqueue_start(m, start_mode, bound);
     launch_ctl_init_flagged(d, s, accel);
+    if (m->use_fused && fused_supported(d)) {
+        // small molecules: the whole iteration of a layer runs inside one persistent CTA (fused_kernels.cu)
+        const int c_f = rt_prof_class(m, "fused_solve");
+        rt_prof_begin(m, c_f, s, 0., 0.);
+        launch_fused_solve(d, s, bound, accel, max_iter, min_err);
+        rt_prof_end(m, c_f, s);
+        CK(cudaStreamSynchronize(s));
+        CK(cudaGetLastError());
+        std::vector<int> itn(d.L);
+        CK(cudaMemcpy(itn.data(), d.iter_nb, sizeof(int) * d.L, cudaMemcpyDeviceToHost));
+        int mx = 0;
+        for (int l = lb; l < le; l++) mx = std::max(mx, itn[l]);
+        m->iters_enqueued += mx;
+        return RT_OK;
+    }
     const int c_ctl = rt_prof_class(m, "controller");
     // n_active after iteration `it` lands in the pinned ring slot (it % RT_RING) + 1; the host reads it one
     // iteration late, so the GPU always has the next iteration queued while the host looks at the count

@@ -81,6 +81,7 @@ struct rt_model {
     cudaStream_t stream = nullptr;
     int* h_n_active = nullptr;     // pinned
     bool has_cloud = false;
+    bool use_fused = true;         // persistent one-CTA-per-layer solver when the matrix fits in shared memory
     // host copies needed by host-side entry points
     std::vector<double> h_energy, h_einst;
     std::vector<int> h_tr_u, h_tr_l, h_grp;
