@@ -13,7 +13,7 @@ One STEP = one slab model taken from "cloud resident in HBM" to "all layers conv
     e2e leg   : rt_cloud_upload (pinned host -> device) + rt_calc_molecular_populations (populations + per-layer
                 status back on the host) -- the call a user of the C ABI makes
 N GPUs: model-per-GPU (BASELINE.json configs[4], no collective): every rank solves its own slab of the same shape
-(same molecule, cloud noise seeded by rank), `value` = N models / max-over-ranks time.  scaling = weak.
+(same molecule and cloud on every rank: fixed per-GPU work), `value` = N models / max-over-ranks time.  scaling = weak.
 `--mode shard` instead partitions ONE slab's layers across ranks (strong scaling; one all_gather of the
 populations at the end).
 """
@@ -59,13 +59,8 @@ def make_problem(args, rank: int):
         name = f"OH slab N={p.N} L={p.L} (BASELINE configs[0])"
     else:
         raise SystemExit(f"unknown --config {args.config}")
-    if rank > 0 and args.mode == "sweep":
-        # model-per-GPU: same molecule and tables, an independently seeded cloud of the same shape
-        rng = np.random.default_rng(977 + rank)
-        lay = dict(p.layers)
-        for k in ("temp_n", "temp_el", "mol_conc", "velg_n"):
-            lay[k] = np.ascontiguousarray(lay[k] * np.exp(0.01 * rng.standard_normal(p.L)))
-        p.layers = lay
+    # model-per-GPU (mode sweep): every rank solves a slab of the SAME shape and content, so per-GPU work is fixed
+    # as N grows (weak scaling); the models are independent -- no collective anywhere on the path
     return p, name
 
 

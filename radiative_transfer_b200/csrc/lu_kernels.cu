@@ -21,6 +21,7 @@
 // Work per layer: (2/3) Np^3 + O(Np^2) flop; HBM traffic ~ sum over outer blocks of 16 m^2 bytes.
 #include "rt_internal.h"
 #include <cfloat>
+#include <cstdlib>
 
 #define PNL_MAXROWS 768 // largest panel height = largest Np
 #ifndef PNL_BIG_R
@@ -49,8 +50,7 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
 
     extern __shared__ double s_tile[]; // [m][33]: coalesced staging of the panel on the way in and out
-    __shared__ double s_val[2][NT / 32];
-    __shared__ int s_idx[2][NT / 32];
+    __shared__ unsigned long long s_key[2][NT / 32];
     __shared__ __align__(16) double s_prow[2][32]; // pivot row (all 32 columns)
     __shared__ int s_pos[64], s_cur[64], s_naff, s_own[2];   // composed permutation (see k_trsm)
     __shared__ short s_slot[NT * R]; // local row -> slot in s_pos, -1 = untouched
@@ -83,33 +83,31 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
         for (int jj = 0; jj < PNL_JB; jj++) {
             const int j = jb + jj;
             const int buf = jj & 1;
-            // ---- (1) pivot search over the rows at positions >= j; ties -> smallest position
-            double best = -1.;
-            int bidx = 0x7fffffff;
+            // ---- (1) pivot search over the rows at positions >= j.  64-bit keys: |a| with its low 10 bits replaced by
+            // 1023 - (position - j): the larger value wins, values equal in their top 54 bits (relative difference
+            // < 2e-13, immaterial for the pivot choice) count as ties -> smallest position, like the scalar loop.
+            // Warp arg-max = two REDUX instructions instead of five shuffle rounds.
+            unsigned long long key = 0ull;
 #pragma unroll
             for (int i = 0; i < R; i++) {
                 if (vp[i] >= j) {
-                    const double v = fabs(x[i][jj]);
-                    if (v > best || (v == best && vp[i] < bidx)) { best = v; bidx = vp[i]; }
+                    const unsigned long long kk = ((unsigned long long)__double_as_longlong(fabs(x[i][jj])) & ~0x3FFull)
+                                                  | (unsigned long long)(1023 - (vp[i] - j));
+                    key = kk > key ? kk : key;
                 }
             }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const double ov = __shfl_xor_sync(0xffffffffu, best, o);
-                const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
-                if (ov > best || (ov == best && oi < bidx)) { best = ov; bidx = oi; }
+            {
+                const unsigned hi = (unsigned)(key >> 32);
+                const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+                const unsigned lo = hi == mhi ? (unsigned)key : 0u;
+                const unsigned mlo = __reduce_max_sync(0xffffffffu, lo);
+                if (lane == 0) s_key[buf][warp] = ((unsigned long long)mhi << 32) | mlo;
             }
-            if (lane == 0) { s_val[buf][warp] = best; s_idx[buf][warp] = bidx; }
             __syncthreads();
-            best = s_val[buf][0];
-            bidx = s_idx[buf][0];
+            key = s_key[buf][0];
 #pragma unroll
-            for (int w = 1; w < NT / 32; w++) {
-                const double ov = s_val[buf][w];
-                const int oi = s_idx[buf][w];
-                if (ov > best || (ov == best && oi < bidx)) { best = ov; bidx = oi; }
-            }
-            const int p = (bidx == 0x7fffffff) ? j : bidx; // all-NaN column: keep the diagonal
+            for (int w = 1; w < NT / 32; w++) { const unsigned long long kk = s_key[buf][w]; key = kk > key ? kk : key; }
+            const int p = j + 1023 - (int)(key & 0x3FFull);
             // ---- (2) interchange of positions j <-> p: the pivot row is published, nothing else moves
 #pragma unroll
             for (int i = 0; i < R; i++) {
@@ -133,7 +131,7 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
             if (t >= jj && jb + t < 32) s_tile[s_own[buf] * 33 + jb + t] = s_prow[buf][t];
             // ---- (3) rank-1 update of the rows below j
             const double piv = s_prow[buf][jj];
-            const double rp = 1. / piv;
+            const double rp = __drcp_rn(piv); // == 1. / piv (correctly rounded), shorter dependency chain
 #pragma unroll
             for (int i = 0; i < R; i++) {
                 if (vp[i] > j) {
@@ -200,7 +198,7 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
 // ------------------------------------------------------------------------------------------------------------
 #define TRSM_THREADS 128
 #define TRSM_LDT 34 // even: rows of the transposed triangles stay 16-byte aligned for double2 loads
-__global__ void __launch_bounds__(TRSM_THREADS) k_trsm(DevModel d, int k0, int c0, int mode, int nlay_bound)
+__global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, int c0, int mode, int nlay_bound)
 {
     const int a = blockIdx.y;
     if (a >= nlay_bound || a >= *d.n_active) return;
@@ -209,6 +207,7 @@ __global__ void __launch_bounds__(TRSM_THREADS) k_trsm(DevModel d, int k0, int c
     __shared__ __align__(16) double Lt[32 * TRSM_LDT];  // Lt[q][r] = L[r][q] of the panel's unit-lower 32x32 block
     __shared__ __align__(16) double Llt[32 * TRSM_LDT]; // mode 2: Llt[q][r] = A[k0+r][k0-32+q]
     __shared__ int s_pos[64], s_cur[64];
+    extern __shared__ double s_u[]; // mode 2: [32][TRSM_THREADS] rows k0-32..k0-1 (U1) of this column tile
     double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
     const int* aff = d.lu_aff + ((size_t)lay * (Np / RT_NB) + k0 / RT_NB) * RT_AFF_STRIDE;
     const int naff = aff[0];
@@ -226,10 +225,9 @@ __global__ void __launch_bounds__(TRSM_THREADS) k_trsm(DevModel d, int k0, int c
     double x[32];
 #pragma unroll
     for (int r = 0; r < 32; r++) x[r] = A[(size_t)(k0 + s_pos[s_cur[r]]) * ld + c];
-    double u[32];
     if (mode == 2) {
 #pragma unroll
-        for (int q = 0; q < 32; q++) u[q] = A[(size_t)(k0 - 32 + q) * ld + c];
+        for (int q = 0; q < 32; q++) s_u[q * TRSM_THREADS + tid] = A[(size_t)(k0 - 32 + q) * ld + c];
     }
     // rows displaced below the block receive ORIGINAL top rows (still untouched in memory: they are rewritten last)
     for (int s = 32; s < naff; s++)
@@ -239,11 +237,12 @@ __global__ void __launch_bounds__(TRSM_THREADS) k_trsm(DevModel d, int k0, int c
 #pragma unroll
         for (int q = 0; q < 32; q++) {
             const double2* lq = reinterpret_cast<const double2*>(Llt + q * TRSM_LDT);
+            const double uq = s_u[q * TRSM_THREADS + tid]; // written by this thread: no barrier needed
 #pragma unroll
             for (int r2 = 0; r2 < 16; r2++) {
                 const double2 l = lq[r2];
-                x[2 * r2] -= l.x * u[q];
-                x[2 * r2 + 1] -= l.y * u[q];
+                x[2 * r2] -= l.x * uq;
+                x[2 * r2 + 1] -= l.y * uq;
             }
         }
     }
@@ -285,8 +284,8 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-template <int K>
-__global__ void __launch_bounds__(256, 2) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int nlay_bound)
+template <int K, int ROWS>
+__global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int nlay_bound)
 {
     const int a = blockIdx.z;
     if (a >= nlay_bound || a >= *d.n_active) return;
@@ -295,19 +294,19 @@ __global__ void __launch_bounds__(256, 2) k_gemm(DevModel d, int i0, int kk0, in
     constexpr int LDA = K + 4;
     extern __shared__ __align__(16) double sm[];
     double* As = sm;                 // [128][LDA]
-    double* Bs = sm + GM_ROWS * LDA; // [K][68]
+    double* Bs = sm + ROWS * LDA; // [K][68]
     double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int r0 = i0 + blockIdx.y * GM_ROWS, cc0 = c0 + blockIdx.x * GM_COLS;
+    const int r0 = i0 + blockIdx.y * ROWS, cc0 = c0 + blockIdx.x * GM_COLS;
     // ---- stage A (rows r0.., K columns at kk0) and B (K rows at kk0, 64 columns at cc0): 16-byte cp.async
     constexpr int ACH = K / 2; // 16-byte chunks per A row
-    for (int e = tid; e < GM_ROWS * ACH; e += 256) {
+    for (int e = tid; e < ROWS * ACH; e += ROWS * 2) {
         const int r = e / ACH, ch = e - r * ACH;
         double* dst = As + r * LDA + 2 * ch;
         if (r0 + r < Np) cp_async16(dst, A + (size_t)(r0 + r) * ld + kk0 + 2 * ch);
         else { dst[0] = 0.; dst[1] = 0.; }
     }
-    for (int e = tid; e < K * (GM_COLS / 2); e += 256) {
+    for (int e = tid; e < K * (GM_COLS / 2); e += ROWS * 2) {
         const int q = e >> 5, ch = e & 31;
         double* dst = Bs + q * GM_LDB + 2 * ch;
         if (cc0 + 2 * ch < c1) cp_async16(dst, A + (size_t)(kk0 + q) * ld + cc0 + 2 * ch);
@@ -367,7 +366,7 @@ __global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int nlay_b
     const int Np = d.Np, ld = d.ld, nb = Np / RT_NB;
     extern __shared__ double ys[]; // [Np]: y, progressively reduced to y - U[:, done] x[done]
     __shared__ double Us[32][33];
-    __shared__ double xb[32];
+    __shared__ __align__(16) double xb[32];
     const double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
     double* __restrict__ xo = d.rhs + (size_t)lay * Np;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -377,12 +376,13 @@ __global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int nlay_b
         for (int rr = warp; rr < 32; rr += BS_THREADS / 32) Us[rr][lane] = A[(size_t)(r0 + rr) * ld + r0 + lane];
         __syncthreads();
         if (warp == 0) {
-            // 32 x 32 upper-triangular solve: x_c = s_c / U_cc, then s_r -= U_rc x_c for r < c
+            // 32 x 32 upper-triangular solve; the scalar loop's divisions become multiplications by reciprocals that
+            // all lanes compute at once (the dependent chain per unknown is shuffle + multiply + fma)
             double s = ys[r0 + lane];
-            const double diag = Us[lane][lane];
+            const double rdiag = __drcp_rn(Us[lane][lane]);
             double xv = 0.;
             for (int c = 31; c >= 0; c--) {
-                const double xc = __shfl_sync(0xffffffffu, s, c) / __shfl_sync(0xffffffffu, diag, c);
+                const double xc = __shfl_sync(0xffffffffu, s * rdiag, c);
                 if (lane == c) xv = xc;
                 if (lane < c) s -= Us[lane][c] * xc;
             }
@@ -390,28 +390,31 @@ __global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int nlay_b
             xo[r0 + lane] = xv;
         }
         __syncthreads();
-        // right-looking update of everything above: ys[r] -= U[r][r0..r0+31] . x_blk, one warp per row
-        const double xl = xb[lane];
-        int r = warp;
-        for (; r + 3 * (BS_THREADS / 32) < r0; r += 4 * (BS_THREADS / 32)) {
-            double v0 = A[(size_t)r * ld + r0 + lane] * xl;
-            double v1 = A[(size_t)(r + BS_THREADS / 32) * ld + r0 + lane] * xl;
-            double v2 = A[(size_t)(r + 2 * (BS_THREADS / 32)) * ld + r0 + lane] * xl;
-            double v3 = A[(size_t)(r + 3 * (BS_THREADS / 32)) * ld + r0 + lane] * xl;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                v0 += __shfl_xor_sync(0xffffffffu, v0, o); v1 += __shfl_xor_sync(0xffffffffu, v1, o);
-                v2 += __shfl_xor_sync(0xffffffffu, v2, o); v3 += __shfl_xor_sync(0xffffffffu, v3, o);
+        // right-looking update of everything above: ys[r] -= U[r][r0..r0+31] . x_blk.  Four threads per row, 8 columns
+        // (64 bytes) each; 128 rows per pass, two passes in flight per thread
+        const int q4 = tid & 3, rsub = tid >> 2;
+        const double2* xq = reinterpret_cast<const double2*>(xb + 8 * q4);
+        const double2 x0 = xq[0], x1 = xq[1], x2 = xq[2], x3 = xq[3];
+        for (int rbase = 0; rbase < r0; rbase += 2 * (BS_THREADS / 4)) {
+            const int ra = rbase + rsub, rb2 = ra + BS_THREADS / 4;
+            double va = 0., vb = 0.;
+            double2 a0, a1, a2, a3, b0, b1, b2, b3;
+            if (ra < r0) {
+                const double2* p = reinterpret_cast<const double2*>(A + (size_t)ra * ld + r0 + 8 * q4);
+                a0 = p[0]; a1 = p[1]; a2 = p[2]; a3 = p[3];
             }
-            if (lane == 0) {
-                ys[r] -= v0; ys[r + BS_THREADS / 32] -= v1; ys[r + 2 * (BS_THREADS / 32)] -= v2; ys[r + 3 * (BS_THREADS / 32)] -= v3;
+            if (rb2 < r0) {
+                const double2* p = reinterpret_cast<const double2*>(A + (size_t)rb2 * ld + r0 + 8 * q4);
+                b0 = p[0]; b1 = p[1]; b2 = p[2]; b3 = p[3];
             }
-        }
-        for (; r < r0; r += BS_THREADS / 32) {
-            double v0 = A[(size_t)r * ld + r0 + lane] * xl;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v0 += __shfl_xor_sync(0xffffffffu, v0, o);
-            if (lane == 0) ys[r] -= v0;
+            if (ra < r0) va = a0.x * x0.x + a0.y * x0.y + a1.x * x1.x + a1.y * x1.y + a2.x * x2.x + a2.y * x2.y + a3.x * x3.x + a3.y * x3.y;
+            if (rb2 < r0) vb = b0.x * x0.x + b0.y * x0.y + b1.x * x1.x + b1.y * x1.y + b2.x * x2.x + b2.y * x2.y + b3.x * x3.x + b3.y * x3.y;
+            va += __shfl_xor_sync(0xffffffffu, va, 1); vb += __shfl_xor_sync(0xffffffffu, vb, 1);
+            va += __shfl_xor_sync(0xffffffffu, va, 2); vb += __shfl_xor_sync(0xffffffffu, vb, 2);
+            if (q4 == 0) {
+                if (ra < r0) ys[ra] -= va;
+                if (rb2 < r0) ys[rb2] -= vb;
+            }
         }
         // the next iteration's barrier after the Us load orders these ys updates before warp 0 reads them
     }
@@ -430,12 +433,22 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
     else k_panel<PNL_BIG_R, PNL_BIG_NT><<<bound, PNL_BIG_NT, smem, s>>>(d, k0, nleft, bound);
 }
 
+// 0: 128x64 tiles, 2 CTAs/SM; 1 (default): 64x64 tiles, 3 CTAs/SM -- 3 % faster at N = 768.  A persistent, cp.async
+// double-buffered variant with C prefetch was measured 25 % SLOWER (3.6 vs 2.9 ms per slab-iteration): at K = 64 the
+// update moves 224 KB per tile through L2 for 4 us of DMMA work, i.e. ~8 TB/s chip-wide -- it is L2-bandwidth-bound,
+// not latency-bound, so deeper pipelining does not help; only a wider outer block (K = 128) would.
+static int g_gemm_mode = 1;
+
 static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk0, int c0, int c1, int bound)
 {
     const dim3 grid((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + GM_ROWS - 1) / GM_ROWS, bound);
     g_rt_launches++;
-    if (K == 32) k_gemm<32><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
-    else k_gemm<64><<<grid, 256, (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
+    if (K == 32) k_gemm<32, 128><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
+    else if (g_gemm_mode == 0) k_gemm<64, 128><<<grid, 256, (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
+    else {
+        const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, bound);
+        k_gemm<64, 64><<<g64, 128, (64 * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
+    }
 }
 
 void launch_lu_solve(rt_model* m, cudaStream_t s, int bound)
@@ -455,7 +468,7 @@ void launch_lu_solve(rt_model* m, cudaStream_t s, int bound)
         const double nc = ld - c0;
         rt_prof_begin(m, c_trsm, s, (mode == 2 ? 3. : 1.) * 32. * 32. * nc, (mode == 2 ? 24. : 16.) * 32. * nc);
         g_rt_launches++;
-        k_trsm<<<dim3((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, bound), TRSM_THREADS, 0, s>>>(d, k0, c0, mode, bound);
+        k_trsm<<<dim3((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, bound), TRSM_THREADS, mode == 2 ? 32 * TRSM_THREADS * sizeof(double) : 0, s>>>(d, k0, c0, mode, bound);
         rt_prof_end(m, c_trsm, s);
     };
     auto gemm = [&](int K, int i0, int kk0, int c0, int c1) {
@@ -490,7 +503,12 @@ cudaError_t lu_kernels_init()
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(k_panel<PNL_BIG_R, PNL_BIG_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 768 * 33 * (int)sizeof(double));
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_gemm<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double));
+    e = cudaFuncSetAttribute(k_gemm<64, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double));
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_gemm<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 36 + 32 * GM_LDB) * (int)sizeof(double));
+    e = cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * TRSM_THREADS * (int)sizeof(double));
+    if (e != cudaSuccess) return e;
+    if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switch
+    e = cudaFuncSetAttribute(k_gemm<64, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (64 * 68 + 64 * GM_LDB) * (int)sizeof(double));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_gemm<32, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 36 + 32 * GM_LDB) * (int)sizeof(double));
 }
