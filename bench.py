@@ -312,21 +312,25 @@ def run_gpu(args):
                    "share": v["ms"] / ms_total}
     traffic = {}
     tf = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tf):
+    if os.path.exists(tf) and args.config == "ch3oh" and args.layers in (None, 0, 200):  # captured on this workload only
         traffic = json.load(open(tf))
     top = max(kern, key=lambda k: kern[k]["ms_per_step"])
+
+    def tbytes(k):
+        t = traffic.get(k)
+        return t.get("bytes") if isinstance(t, dict) else t
 
     def roof(k):
         v, pv = kern[k], prof[k]
         ai = pv["flops"] / max(pv["bytes"], 1.0)
         if ai > fp64_peak * 1e3 / hbm_peak:  # flop/byte above the machine balance -> FP64 pipe bound
             return {"kernel": k, "bound": "tensor", "achieved": v["tflops"], "peak": fp64_peak, "unit": "TFLOP/s",
-                    "frac": v["tflops"] / fp64_peak, "traffic": traffic.get(k),
+                    "frac": v["tflops"] / fp64_peak, "traffic": tbytes(k), "traffic_detail": traffic.get(k),
                     "peak_source": f"FP64 measured in this run by rt_device_fp64_peak: DFMA {dfma:.1f}, DMMA {dmma:.1f} TFLOP/s "
                                    "(MEASURED_PEAKS.json has no FP64 figure; the LU runs on the FP64 pipe, not bf16 tcgen05)",
                     "share_of_step": v["share"]}
         return {"kernel": k, "bound": "hbm", "achieved": v["gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": v["gbs"] / hbm_peak,
-                "traffic": traffic.get(k), "peak_source": hbm_src, "share_of_step": v["share"]}
+                "traffic": tbytes(k), "traffic_detail": traffic.get(k), "peak_source": hbm_src, "share_of_step": v["share"]}
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,

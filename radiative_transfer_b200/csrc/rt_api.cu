@@ -563,8 +563,14 @@ static rt_status solve_range(rt_model* m, int lb, int le, int start_mode, int ma
         std::vector<int> itn(d.L);
         CK(cudaMemcpy(itn.data(), d.iter_nb, sizeof(int) * d.L, cudaMemcpyDeviceToHost));
         int mx = 0;
-        for (int l = lb; l < le; l++) mx = std::max(mx, itn[l]);
+        double layer_iters = 0.;
+        for (int l = lb; l < le; l++) { mx = std::max(mx, itn[l]); layer_iters += itn[l]; }
         m->iters_enqueued += mx;
+        // algorithmic work of the launch, known only now: per layer-iteration one LU + two triangular solves +
+        // the residual product; HBM bytes only when C(layer) does not fit beside M in shared memory (Np > 96)
+        const double n = d.N;
+        m->prof_flops[c_f] += layer_iters * (2. / 3. * n * n * n + 4. * n * n);
+        m->prof_bytes[c_f] += layer_iters * (d.Np > 96 ? 8. * n * n : 0.) + (double)(le - lb) * 8. * n * n;
         return RT_OK;
     }
     const int c_ctl = rt_prof_class(m, "controller");

@@ -1,0 +1,37 @@
+"""Summarise an .ncu-rep (read here with `ncu -i`) into a small CSV for profiles/: one row per captured launch
+with duration, DRAM bytes, L2 hit rate, pipe utilisation, occupancy and the top warp-stall reasons."""
+import csv, subprocess, sys, io
+
+METRICS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+           "dram__throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+           "lts__t_sector_hit_rate.pct", "sm__warps_active.avg.pct_of_peak_sustained_active",
+           "launch__registers_per_thread", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
+           "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+           "sm__pipe_tensor_op_dmma_cycles_active.avg.pct_of_peak_sustained_active",
+           "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+           "smsp__issue_active.avg.pct",
+           "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+           "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+           "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+           "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+           "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+           "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio",
+           "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio"]
+
+
+def main(rep, out):
+    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(txt)))
+    h, units = rows[0], rows[1]
+    idx = {n: i for i, n in enumerate(h)}
+    cols = ["ID", "Kernel Name", "Grid Size", "Block Size"] + [m for m in METRICS if m in idx]
+    with open(out, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow([c + (" [" + units[idx[c]] + "]" if units[idx[c]] else "") for c in cols])
+        for r in rows[2:]:
+            w.writerow([r[idx[c]] for c in cols])
+    print(out, len(rows) - 2, "launches")
+
+
+if __name__ == "__main__":
+    main(sys.argv[1], sys.argv[2])
