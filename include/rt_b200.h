@@ -164,6 +164,10 @@ typedef struct rt_layer_soa {
     const double* vel_n;    /* post-pass only */
     const double* dust_conc; /* [L][dust_ncomp] */
     double height;          /* cloud_data::get_height(), post-pass only */
+    /* Optional (ABI 2): the state an iteration_scheme_lvg object holds after its setters ran, passed through verbatim so a
+     * scheme subclass reproduces it bit for bit.  NULL = derived from the fields above. */
+    const double* vel_width;    /* [L] iteration_lvg.cpp:65; NULL: sqrt(2kT/m + vel_turb^2) */
+    const double* partner_conc; /* [L][nb_neutral_tables + nb_electron_tables] coll_partn_conc of set_gas_param; NULL: species rule */
 } rt_layer_soa;
 
 /* Per-layer outcome == the public members of iteration_control after calculate_populations

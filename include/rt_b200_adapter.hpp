@@ -242,4 +242,101 @@ inline bool calc_molecular_populations_gpu(cloud_data* cloud, iteration_scheme_l
     return true;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Per-call drop-in: a scheme object whose step runs on the GPU.  It IS an iteration_scheme_lvg (or
+// iteration_scheme_line_overlap), so the reference's three per-layer setters, its `iteration_control<T>` controller
+// (duck-typed on get_vector_dim() / calc_new_pop(), iteration_control.h:101,210) and lim_luminosity_lvg
+// (intensity_calc, maser_luminosity.cpp:54-58) keep working on it unchanged:
+//
+//     iteration_scheme_lvg_gpu scheme(data_path, verbosity);          // instead of iteration_scheme_lvg
+//     scheme.set_dust_model(dust);  scheme.init_molecule_data(levels, einst, coll);
+//     iteration_control<iteration_scheme_lvg_gpu> ctl(&scheme);       // the reference's controller, GPU steps
+//     scheme.set_vel_grad(..); scheme.set_dust_parameters(..); scheme.set_parameters(..);   // radiative_transfer.cpp:238-242
+//     ctl.calculate_populations(pop, max_iter, accel);
+//
+// The layer state is PULLED from the base object's protected members at every call (temp_n, temp_el, mol_conc, vel_width,
+// vel_grad, coll_partn_conc, dgrain_conc), so it does not matter through which pointer type the setters were called;
+// vel_width and the partner concentrations go through rt_layer_soa::vel_width / partner_conc verbatim.
+// calc_new_pop is not virtual in the reference (iteration_lvg.h:53): the GPU step is taken when the controller is
+// instantiated on this type; through a base pointer the virtual operator() below still assembles on the GPU and the
+// base class's own LU finishes the step.  One layer per call: this is the fidelity path (step-by-step comparison with
+// the CPU classes), the throughput path is calc_molecular_populations_gpu above.
+template <class Base> class scheme_gpu : public Base
+{
+    rt_model* model_ = nullptr;
+    int device_, rule_;
+    flat_model fm_;
+    std::vector<double> state_; // what the resident 1-layer cloud was built from
+
+    bool sync()
+    {
+        if (!model_) {
+            flatten_model(this, this->diagram, this->einst_coeff, this->coll_trans, rule_, fm_);
+            rt_status rc = rt_model_create(&fm_.desc, device_, &model_);
+            if (rc != RT_OK) { std::cout << "rt_b200: " << rt_status_string(rc) << ": " << rt_last_error(nullptr) << std::endl; model_ = nullptr; return false; }
+            state_.clear();
+        }
+        const int K = fm_.desc.nb_neutral_tables + fm_.desc.nb_electron_tables;
+        std::vector<double> st = {this->temp_n, this->temp_el, this->mol_conc, this->vel_width, this->vel_grad};
+        for (int k = 0; k < K; k++) st.push_back(this->coll_partn_conc ? this->coll_partn_conc[k] : 0.);
+        st.insert(st.end(), this->dgrain_conc.begin(), this->dgrain_conc.end());
+        bool same = st.size() == state_.size();
+        for (size_t i = 0; same && i < st.size(); i++) same = memcmp(&st[i], &state_[i], sizeof(double)) == 0;
+        if (same) return true;
+        const double zero = 0.;
+        // vel_turb only feeds the post-pass; recovered from vel_width for completeness (iteration_lvg.cpp:65 inverted)
+        const double vt2 = this->vel_width * this->vel_width - 2. * fm_.desc.params.boltzmann_constant * this->temp_n / fm_.desc.mol_mass;
+        const double vt = vt2 > 0. ? sqrt(vt2) : 0.;
+        rt_layer_soa s;
+        memset(&s, 0, sizeof s);
+        s.nb_lay = 1; s.dust_ncomp = (int)this->dgrain_conc.size();
+        s.temp_n = &st[0]; s.temp_el = &st[1]; s.mol_conc = &st[2]; s.vel_width = &st[3]; s.velg_n = &st[4];
+        s.el_conc = s.h_conc = s.ph2_conc = s.oh2_conc = s.he_conc = &zero; // superseded by partner_conc
+        s.partner_conc = st.data() + 5;
+        s.vel_turb = &vt;
+        s.dust_conc = st.data() + 5 + K;
+        rt_status rc = rt_cloud_upload(model_, &s);
+        if (rc != RT_OK) { std::cout << "rt_b200: " << rt_status_string(rc) << ": " << rt_last_error(model_) << std::endl; state_.clear(); return false; }
+        state_.swap(st);
+        return true;
+    }
+    void fail(const char* what) const
+    {
+        std::cout << "rt_b200: " << what << " failed: " << rt_last_error(model_) << std::endl;
+        exit(1); // the reference's own reaction to a fatal condition (iteration_lvg.cpp:82-83)
+    }
+
+public:
+    scheme_gpu(const std::string& data_path, int verbosity = 1, int device = 0, int species_rule = -1)
+        : Base(data_path, verbosity), device_(device), rule_(species_rule) {}
+    ~scheme_gpu() { if (model_) rt_model_destroy(model_); }
+    scheme_gpu(const scheme_gpu&) = delete;
+    scheme_gpu& operator=(const scheme_gpu&) = delete;
+
+    void init_molecule_data(const energy_diagram* d, const einstein_coeff* e, const collisional_transitions* c)
+    {
+        Base::init_molecule_data(d, e, c);
+        if (model_) { rt_model_destroy(model_); model_ = nullptr; } // molecule changed: rebuilt at the next call
+    }
+    // == iteration_scheme_lvg::calc_new_pop (iteration_lvg.cpp:87-110): assembly + LU solve on the GPU
+    void calc_new_pop(double* old_pop, double* new_pop, double& eq_error)
+    {
+        if (!sync() || rt_step(model_, old_pop, new_pop, &eq_error) != RT_OK) fail("rt_step");
+    }
+    // == operator() (iteration_lvg.cpp:112-161, :348-426): matrix into the base object's `matrix`, residual into df
+    void operator()(int dim, double* level_pop, double* df)
+    {
+        if (dim != this->nb_mol_lev || !sync() || rt_assemble(model_, level_pop, *this->matrix, df) != RT_OK) fail("rt_assemble");
+    }
+    // == intensity_calc (iteration_lvg.cpp:163-185; overlap scheme :503-): dimensionless mean intensity of one line
+    void intensity_calc(int upl, int lowl, double* lev_pop, double& intensity) const
+    {
+        scheme_gpu* self = const_cast<scheme_gpu*>(this);
+        if (!self->sync() || rt_intensity(model_, 0, upl, lowl, lev_pop, &intensity) != RT_OK) fail("rt_intensity");
+    }
+    rt_model* model() { return sync() ? model_ : nullptr; }
+};
+typedef scheme_gpu<iteration_scheme_lvg> iteration_scheme_lvg_gpu;
+typedef scheme_gpu<iteration_scheme_line_overlap> iteration_scheme_line_overlap_gpu;
+
 } // namespace rt_b200

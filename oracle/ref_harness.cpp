@@ -753,5 +753,102 @@ int ref_adapter_calc_molecular_populations(const rt_model_desc* d, const rt_laye
     return ok ? 0 : 1;
 }
 
+
+} // extern "C"
+
+// ---- the per-call drop-in (rt_b200::scheme_gpu): the REFERENCE's controller drives GPU steps ---------------------------
+namespace {
+template <class S> struct counting_any {
+    S* s;
+    int calls;
+    int get_vector_dim() { return s->get_vector_dim(); }
+    void calc_new_pop(double* o, double* n, double& e) { calls++; s->calc_new_pop(o, n, e); }
+};
+
+template <class S> int gpu_scheme_solve(ref_ctx* c, const rt_model_desc* d, double* pop, int start_mode, int max_iter, double min_err,
+                                        int accel, rt_layer_status* st, int lay_begin, int lay_end, int device)
+{
+    const int N = c->N;
+    S s(c->tmp, 0, device, d->species_rule);
+    s.set_dust_model(c->dust);
+    s.init_molecule_data(c->diagram, c->einst, c->coll);
+    counting_any<S> cs{&s, 0};
+    iteration_control<counting_any<S> > ctl(&cs);
+    for (int l = lay_begin; l < lay_end; l++) {
+        const cloud_layer cl = c->cloud->lay_array[l];
+        iteration_scheme_lvg* base = &s; // the setters are called the way radiative_transfer.cpp:238-242 calls them
+        base->set_vel_grad(cl.velg_n);
+        std::vector<double> dc(cl.dust_grain_conc), dt(cl.dust_grain_temp);
+        base->set_dust_parameters(dc, dt);
+        base->set_parameters(cl.temp_n, cl.temp_el, cl.el_conc, cl.h_conc, cl.ph2_conc, cl.oh2_conc, cl.he_conc, cl.mol_conc, cl.vel_turb);
+        double* p = pop + (size_t)l * N;
+        if (start_mode == RT_START_BOUNDARY)
+            boundary_layer_populations(p, c->diagram, c->einst, c->coll, cl.temp_n, cl.temp_el, cl.el_conc, cl.h_conc, cl.ph2_conc,
+                                       cl.oh2_conc, cl.he_conc);
+        else if (start_mode == RT_START_LTE) boltzmann_populations(cl.temp_n, p, c->diagram);
+        cs.calls = 0;
+        const bool found = ctl.calculate_populations(p, max_iter, min_err, accel != 0, 0);
+        if (st) {
+            st[l].iters = cs.calls; st[l].converged = found ? 1 : 0;
+            st[l].eq_error = ctl.eq_error; st[l].pop_error = ctl.pop_error; st[l].rel_error = ctl.rel_error;
+        }
+    }
+    return 0;
+}
+
+// operator() and intensity_calc of the GPU scheme called through a BASE pointer (virtual dispatch), layer l
+template <class S> int gpu_scheme_probe(ref_ctx* c, const rt_model_desc* d, int l, const double* pop, double* matrix, double* df,
+                                        double* new_pop, double* eq_err, int n, const int* up, const int* low, double* J, int device)
+{
+    const int N = c->N;
+    S s(c->tmp, 0, device, d->species_rule);
+    iteration_scheme_lvg* base = &s;
+    base->set_dust_model(c->dust);
+    base->init_molecule_data(c->diagram, c->einst, c->coll);
+    const cloud_layer cl = c->cloud->lay_array[l];
+    base->set_vel_grad(cl.velg_n);
+    std::vector<double> dc(cl.dust_grain_conc), dt(cl.dust_grain_temp);
+    base->set_dust_parameters(dc, dt);
+    base->set_parameters(cl.temp_n, cl.temp_el, cl.el_conc, cl.h_conc, cl.ph2_conc, cl.oh2_conc, cl.he_conc, cl.mol_conc, cl.vel_turb);
+    std::vector<double> p(pop, pop + N);
+    (*base)(N, p.data(), df);
+    struct peek : public S { using S::S; double** mat() { return this->matrix; } };
+    memcpy(matrix, *static_cast<peek*>(static_cast<S*>(base))->mat(), sizeof(double) * N * N);
+    // base-class calc_new_pop: GPU assembly through the virtual operator(), then the reference's own LU
+    base->calc_new_pop(p.data(), new_pop, *eq_err);
+    for (int i = 0; i < n; i++) base->intensity_calc(up[i], low[i], p.data(), J[i]);
+    return 0;
+}
+} // namespace
+
+extern "C" {
+
+int ref_adapter_scheme_solve(const rt_model_desc* d, const rt_layer_soa* lay, double* pop, int start_mode, int max_iter, double min_err,
+                             int accel, rt_layer_status* st, int lay_begin, int lay_end, int device)
+{
+    ref_ctx* c = build_ctx(d, lay);
+    if (lay_end < 0 || lay_end > c->L) lay_end = c->L;
+    null_buf nb;
+    cout_redirect quiet(&nb);
+    const int rc = c->overlap
+        ? gpu_scheme_solve<rt_b200::iteration_scheme_line_overlap_gpu>(c, d, pop, start_mode, max_iter, min_err, accel, st, lay_begin, lay_end, device)
+        : gpu_scheme_solve<rt_b200::iteration_scheme_lvg_gpu>(c, d, pop, start_mode, max_iter, min_err, accel, st, lay_begin, lay_end, device);
+    delete c;
+    return rc;
+}
+
+int ref_adapter_scheme_probe(const rt_model_desc* d, const rt_layer_soa* lay, int l, const double* pop, double* matrix, double* df,
+                             double* new_pop, double* eq_err, int n, const int* up, const int* low, double* J, int device)
+{
+    ref_ctx* c = build_ctx(d, lay);
+    null_buf nb;
+    cout_redirect quiet(&nb);
+    const int rc = c->overlap
+        ? gpu_scheme_probe<rt_b200::iteration_scheme_line_overlap_gpu>(c, d, l, pop, matrix, df, new_pop, eq_err, n, up, low, J, device)
+        : gpu_scheme_probe<rt_b200::iteration_scheme_lvg_gpu>(c, d, l, pop, matrix, df, new_pop, eq_err, n, up, low, J, device);
+    delete c;
+    return rc;
+}
+
 } // extern "C"
 #endif

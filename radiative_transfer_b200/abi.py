@@ -68,7 +68,7 @@ class rt_layer_soa(C.Structure):
     _fields_ = [("nb_lay", C.c_int), ("dust_ncomp", C.c_int)] + [
         (n, c_double_p) for n in ("temp_n", "temp_el", "el_conc", "h_conc", "ph2_conc", "oh2_conc", "he_conc",
                                   "mol_conc", "vel_turb", "velg_n", "dz", "vel_n", "dust_conc")
-    ] + [("height", C.c_double)]
+    ] + [("height", C.c_double), ("vel_width", c_double_p), ("partner_conc", c_double_p)]
 
 
 class rt_layer_status(C.Structure):

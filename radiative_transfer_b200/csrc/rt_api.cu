@@ -35,6 +35,13 @@ template <class T> static T* dev_alloc(rt_model* m, size_t n, bool cloud, bool z
 {
     void* p = nullptr;
     if (n == 0) n = 1;
+    if (cloud && m->cloud_reuse) {
+        // same layer count as the resident cloud: every buffer has the size it had, in the same order; a parameter sweep
+        // then never touches the allocator (cudaMalloc/cudaFree serialise across the GPUs of a node)
+        p = m->cloud_allocs[m->cloud_slot++];
+        if (zero) cudaMemsetAsync(p, 0, n * sizeof(T), m->stream);
+        return (T*)p;
+    }
     if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) { m->last_error = "cudaMalloc failed"; return nullptr; }
     if (zero) cudaMemsetAsync(p, 0, n * sizeof(T), m->stream);
     (cloud ? m->cloud_allocs : m->allocs).push_back(p);
@@ -85,7 +92,7 @@ const char* rt_status_string(rt_status s)
 }
 
 const char* rt_last_error(const rt_model* m) { return m ? m->last_error.c_str() : g_create_error.c_str(); }
-int rt_abi_version(void) { return 1; }
+int rt_abi_version(void) { return 2; }
 
 } // extern "C"
 
@@ -408,27 +415,38 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
     if (lay->dust_ncomp != m->d.ncomp) { m->last_error = "inconsistency in the interstellar dust data"; return RT_ERR_DUST_INCONSISTENT; }
     CK(cudaSetDevice(m->device));
     CK(cudaStreamSynchronize(m->stream));
-    free_cloud(m);
     DevModel& d = m->d;
     const int L = lay->nb_lay, N = d.N, Np = d.Np, K = d.K;
+    m->cloud_reuse = m->has_cloud && d.L == L;
+    m->cloud_slot = 0;
+    if (!m->cloud_reuse) free_cloud(m);
+    m->has_cloud = false; // until this upload completes
     d.L = L;
     // the three per-layer setters, radiative_transfer.cpp:238-242
     std::vector<double> vw(L), conc((size_t)L * K, 0.);
     std::vector<int> tidx((size_t)L * K, 0);
     // temperature grids are needed on the host for locate(); fetch them back from the tables
-    std::vector<std::vector<double>> tg(K);
-    for (int k = 0; k < K; k++) {
-        tg[k].resize(d.tab[k].jmax);
-        CK(cudaMemcpy(tg[k].data(), d.tab[k].tgrid, sizeof(double) * d.tab[k].jmax, cudaMemcpyDeviceToHost));
+    std::vector<std::vector<double>>& tg = m->h_tgrid;
+    if ((int)tg.size() != K) {
+        tg.assign(K, {});
+        for (int k = 0; k < K; k++) {
+            tg[k].resize(d.tab[k].jmax);
+            CK(cudaMemcpy(tg[k].data(), d.tab[k].tgrid, sizeof(double) * d.tab[k].jmax, cudaMemcpyDeviceToHost));
+        }
     }
     for (int l = 0; l < L; l++) {
         // iteration_lvg.cpp:65
-        vw[l] = pow(2. * d.prm.boltzmann_constant * lay->temp_n[l] / d.mol_mass + lay->vel_turb[l] * lay->vel_turb[l], 0.5);
+        vw[l] = lay->vel_width ? lay->vel_width[l]
+                               : pow(2. * d.prm.boltzmann_constant * lay->temp_n[l] / d.mol_mass + lay->vel_turb[l] * lay->vel_turb[l], 0.5);
         double* c = &conc[(size_t)l * K];
         int* ix = &tidx[(size_t)l * K];
         // set_gas_param: coll_rates.cpp:152-174 + coll_rates_ch3oh.cpp:472-481, coll_rates_oh.cpp:380-389, coll_rates_h2o.cpp:515-527
         for (int k = 0; k < d.nb1; k++) ix[k] = coll_locate(tg[k].data(), d.tab[k].jmax, lay->temp_n[l]);
-        for (int k = d.nb1; k < d.nb2; k++) { c[k] = lay->el_conc[l]; ix[k] = coll_locate(tg[k].data(), d.tab[k].jmax, lay->temp_el[l]); }
+        for (int k = d.nb1; k < d.nb2; k++) { c[k] = lay->el_conc ? lay->el_conc[l] : 0.; ix[k] = coll_locate(tg[k].data(), d.tab[k].jmax, lay->temp_el[l]); }
+        if (lay->partner_conc) {
+            for (int k = 0; k < K; k++) c[k] = lay->partner_conc[(size_t)l * K + k];
+            continue;
+        }
         const double he = lay->he_conc[l], ph2 = lay->ph2_conc[l], oh2 = lay->oh2_conc[l], h = lay->h_conc[l];
         switch (d.rule) {
         case RT_RULE_CH3OH: case RT_RULE_OH_HF: c[0] = he; c[1] = ph2; c[2] = oh2; break;
@@ -468,9 +486,11 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
     d.eq_bits = dev_alloc<unsigned long long>(m, L, true);
     d.n_active = dev_alloc<int>(m, 4, true);
     if (!d.Cmat || !d.Mmat || !d.pop || !d.hist_pop || !d.hist_res || !d.n_active || !m->last_error.empty()) {
+        m->cloud_reuse = false;
         free_cloud(m);
         return RT_ERR_NOMEM;
     }
+    m->cloud_reuse = false;
     m->h_status.assign(L, rt_layer_status{});
     // K0: collisional matrix of every layer, once (it does not depend on the populations)
     const int c0 = rt_prof_class(m, "coll_matrix");

@@ -78,6 +78,9 @@ struct rt_model {
     std::string last_error;
     std::vector<void*> allocs;     // every cudaMalloc, freed in rt_model_destroy
     std::vector<void*> cloud_allocs;
+    bool cloud_reuse = false;      // rt_cloud_upload with an unchanged layer count hands the resident buffers out again
+    size_t cloud_slot = 0;
+    std::vector<std::vector<double>> h_tgrid; // host copy of the collision tables' temperature grids (set_gas_param)
     cudaStream_t stream = nullptr;
     int* h_n_active = nullptr;     // pinned
     bool has_cloud = false;

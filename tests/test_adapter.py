@@ -51,3 +51,58 @@ def test_reference_objects_through_adapter_on_gpu(adapter, ref, problems, name, 
     assert np.all(st["converged"][solid] == 1)
     assert np.all(np.abs(st["iters"] - st_o["iters"])[solid] <= 1)
     assert rel_err(pop[solid], pop_o[solid], 1e-30) < 1e-6
+
+
+# ---- rt_b200::scheme_gpu: the per-call drop-in (a scheme object whose step runs on the GPU) ----------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["ch3oh_small", "oh_overlap", "generic"])
+def test_reference_controller_drives_gpu_scheme(adapter, ref, problems, name):
+    """iteration_control<T> of the reference, instantiated on the GPU scheme type: every calc_new_pop is one rt_step."""
+    from radiative_transfer_b200 import abi
+    p = problems(name, 3)
+    d, h1 = p.desc()
+    s, h2 = p.layer_soa()
+    pop = np.zeros((p.L, p.N))
+    st = np.zeros(p.L, dtype=abi.STATUS_DTYPE)
+    max_iter = min(p.max_iter, 400)
+    adapter.ref_adapter_scheme_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int,
+                                                 C.c_void_p, C.c_int, C.c_int, C.c_int]
+    rc = adapter.ref_adapter_scheme_solve(C.addressof(d), C.addressof(s), pop.ctypes.data, abi.RT_START_BOUNDARY, max_iter, 1e-5,
+                                          int(p.accel), st.ctypes.data, 0, -1, 0)
+    assert rc == 0
+    pop_o, st_o, _ = ref.solve(p, start_mode=abi.RT_START_BOUNDARY, max_iter=max_iter, retry=False)
+    solid = (st_o["converged"] == 1) & (st_o["iters"] < max_iter - 20)
+    assert solid.any()
+    assert np.all(st["converged"][solid] == 1)
+    assert np.all(np.abs(st["iters"] - st_o["iters"])[solid] <= 1)
+    assert rel_err(pop[solid], pop_o[solid], 1e-30) < 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["ch3oh_small", "oh_overlap", "h2o_small"])
+def test_gpu_scheme_virtuals_through_base_pointer(adapter, ref, problems, name):
+    """operator(), calc_new_pop (base LU over the GPU-assembled matrix) and intensity_calc via iteration_scheme_lvg*."""
+    p = problems(name, 3)
+    d, h1 = p.desc()
+    s, h2 = p.layer_soa()
+    lay = 1
+    pop = ref.boundary(p)
+    N = p.N
+    iu, il = np.nonzero(np.tril(p.einst, -1) > 0)
+    sel = np.linspace(0, iu.shape[0] - 1, min(40, iu.shape[0])).astype(int)
+    up = np.ascontiguousarray(iu[sel], dtype=np.int32); low = np.ascontiguousarray(il[sel], dtype=np.int32)
+    M = np.zeros((N, N)); df = np.zeros(N); new = np.zeros(N); eq = C.c_double(); J = np.zeros(len(up))
+    adapter.ref_adapter_scheme_probe.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                 C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    rc = adapter.ref_adapter_scheme_probe(C.addressof(d), C.addressof(s), lay, pop[lay].ctypes.data, M.ctypes.data, df.ctypes.data,
+                                          new.ctypes.data, C.addressof(eq), len(up), up.ctypes.data, low.ctypes.data, J.ctypes.data, 0)
+    assert rc == 0
+    M_o, df_o = ref.assemble(p, pop)
+    new_o, eq_o = ref.step(p, pop)
+    J_o = ref.intensity(p, lay, up, low, pop[lay])
+    scale = np.abs(M_o[lay]).max()
+    assert np.abs(M - M_o[lay]).max() <= 1e-12 * scale
+    assert np.abs(df - df_o[lay]).max() <= 1e-12 * max(np.abs(df_o[lay]).max(), 1e-300) + 1e-13 * scale
+    assert rel_err(new, new_o[lay], 1e-30) < 1e-9
+    assert abs(eq.value - eq_o[lay]) <= 1e-9 * abs(eq_o[lay]) + 1e-13 * scale
+    assert np.allclose(J, J_o, rtol=1e-10, atol=1e-300)
