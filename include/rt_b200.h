@@ -39,7 +39,9 @@ enum {
     RT_RULE_GENERIC = 0, /* collisional_transitions::get_rate_neutrals        coll_rates.cpp:181-197        */
     RT_RULE_CH3OH = 1,   /* ch3oh_collisions::get_rate_neutrals               coll_rates_ch3oh.cpp:484-533  */
     RT_RULE_OH_HF = 2,   /* oh_hf_collisions::get_rate_neutrals               coll_rates_oh.cpp:392-407     */
-    RT_RULE_H2O = 3      /* h2o_collisions::get_rate_neutrals                 coll_rates_h2o.cpp:530-548    */
+    RT_RULE_H2O = 3,     /* h2o_collisions::get_rate_neutrals                 coll_rates_h2o.cpp:530-548    */
+    RT_RULE_NH3 = 4,     /* nh3_collisions::get_rate_neutrals (He, p-H2, o-H2, H) coll_rates_nh3.cpp:261-290     */
+    RT_RULE_H2CO = 5     /* h2co_collisions::get_rate_neutrals (He, p-H2, o-H2) coll_rates_h2co.cpp:160-185      */
 };
 
 /* Iteration scheme */
@@ -71,6 +73,7 @@ typedef struct rt_params {
     double speed_of_light;        /* cm/s                                                            */
     double eight_pi;
     double onedivby_sqrt_pi;
+    double planck_constant;       /* erg s (ABI 2; rt_lim_luminosity: temp_sat, transition_data.cpp:479) */
 } rt_params;
 
 /* One collision_data table (coll_rates.h:12-41).  coeff is [imax][jmax] row-major, imax = nb_lev*(nb_lev-1)/2,
@@ -256,6 +259,22 @@ rt_status rt_maser_postpass(rt_model* m, const double* pop, int nb_trans, const 
                             int nb_freq, int nb_aspect, double delta_aspect, double velocity_shift,
                             double* inv_arr, double* gain_arr, double* scalars /*[nb_trans][5]*/,
                             double* tau_vs_aspect, double* tau_vs_freq);
+
+/* Limiting maser luminosity and pump/loss rates: lim_luminosity_lvg (maser_luminosity.cpp:7-106),
+ * calc_exc_temp (transition_data.cpp:225-237) and calc_saturation_depth (transition_data.cpp:456-483) for each listed
+ * transition (up[i] > low[i]).  pop HOST [L*N].  Per transition and layer, all [nb_trans][L], any may be NULL:
+ * lum_arr, pump_eff_arr, loss_rate_arr, pump_rate_arr, emiss_coeff_arr, exc_temp_arr; per transition: lum [nb_trans].
+ * layer0_intensity != 0 reproduces the reference literally: the mean intensity inside the radiative loss terms is
+ * evaluated with the populations of LAYER 0 and the gas parameters of the current layer (intensity_calc is handed the
+ * base pointer `level_pop`, maser_luminosity.cpp:54,58); 0 uses the populations of the current layer.
+ * Saturation: with lay_nb_hg [nb_trans] (layer of the highest gain, scalars[4] of rt_maser_postpass) and a beaming
+ * factor, tau_sat / temp_sat [nb_trans] are filled for transitions whose excitation temperature in that layer is
+ * negative and left at 0 otherwise; lay_nb_hg == NULL skips it.
+ * Needs the cloud uploaded with the plain rt_layer_soa fields (ph2_conc, oh2_conc, dz, height). */
+rt_status rt_lim_luminosity(rt_model* m, const double* pop, int nb_trans, const int* up, const int* low,
+                            int layer0_intensity, double* lum_arr, double* pump_eff_arr, double* loss_rate_arr,
+                            double* pump_rate_arr, double* emiss_coeff_arr, double* exc_temp_arr, double* lum,
+                            const int* lay_nb_hg, double beaming_factor, double* tau_sat, double* temp_sat);
 
 #ifdef __cplusplus
 }

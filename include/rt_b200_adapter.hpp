@@ -13,18 +13,22 @@
 #include <cmath>
 #include <cstring>
 #include <iostream>
+#include <list>
 #include <string>
 #include <vector>
 
 #include "cloud_data.h"
 #include "coll_rates.h"
 #include "coll_rates_ch3oh.h"
+#include "coll_rates_h2co.h"
 #include "coll_rates_h2o.h"
+#include "coll_rates_nh3.h"
 #include "coll_rates_oh.h"
 #include "dust_model.h"
 #include "iteration_lvg.h"
 #include "lvg_method_functions.h"
 #include "spectroscopy.h"
+#include "transition_data.h"
 
 #include "rt_b200.h"
 
@@ -77,6 +81,8 @@ inline int species_rule_of(const collisional_transitions* coll)
     if (dynamic_cast<const ch3oh_collisions*>(coll)) return RT_RULE_CH3OH;
     if (dynamic_cast<const oh_hf_collisions*>(coll)) return RT_RULE_OH_HF;
     if (dynamic_cast<const h2o_collisions*>(coll)) return RT_RULE_H2O;
+    if (dynamic_cast<const nh3_collisions*>(coll)) return RT_RULE_NH3;
+    if (dynamic_cast<const h2co_collisions*>(coll)) return RT_RULE_H2CO;
     return RT_RULE_GENERIC;
 }
 
@@ -239,6 +245,50 @@ inline bool calc_molecular_populations_gpu(cloud_data* cloud, iteration_scheme_l
         std::cout << std::endl;
     }
     if (status) memcpy(status, st.data(), sizeof(rt_layer_status) * st.size());
+    return true;
+}
+
+// Drop-in for lim_luminosity_lvg (maser_luminosity.cpp:7-106): same arguments; fills lum, lum_arr, pump_eff_arr,
+// loss_rate_arr, pump_rate_arr, emiss_coeff_arr of every entry of container->data.  literal_layer0 = true keeps the
+// reference's behaviour of evaluating J of the loss terms with the populations of layer 0 (see rt_lim_luminosity).
+// calc_saturation_depth of the container can be called afterwards exactly as before.
+inline bool lim_luminosity_lvg_gpu(iteration_scheme_lvg* calc_scheme, transition_data_container* container, const cloud_data* cloud,
+                                   const energy_diagram* diagram, const einstein_coeff* einst_coeff, collisional_transitions* coll_trans,
+                                   double* level_pop, int device = 0, int species_rule = -1, bool literal_layer0 = true)
+{
+    const int L = cloud->nb_lay, T = (int)container->data.size();
+    if (T == 0) return true;
+    flat_model fm;
+    flat_cloud fc;
+    flatten_model(calc_scheme, diagram, einst_coeff, coll_trans, species_rule, fm);
+    flatten_cloud(cloud, fc);
+    rt_model* m = nullptr;
+    rt_status rc = rt_model_create(&fm.desc, device, &m);
+    if (rc != RT_OK) { std::cout << "rt_b200: " << rt_status_string(rc) << ": " << rt_last_error(nullptr) << std::endl; return false; }
+    std::vector<int> up(T), low(T);
+    int t = 0;
+    for (std::list<transition_data>::iterator it = container->data.begin(); it != container->data.end(); ++it, ++t) {
+        up[t] = it->trans->up_lev.nb; low[t] = it->trans->low_lev.nb;
+    }
+    std::vector<double> a[5], lum(T);
+    for (auto& v : a) v.resize((size_t)T * L);
+    rc = rt_cloud_upload(m, &fc.soa);
+    if (rc == RT_OK)
+        rc = rt_lim_luminosity(m, level_pop, T, up.data(), low.data(), literal_layer0 ? 1 : 0, a[0].data(), a[1].data(), a[2].data(),
+                               a[3].data(), a[4].data(), nullptr, lum.data(), nullptr, 1., nullptr, nullptr);
+    if (rc != RT_OK) std::cout << "rt_b200: " << rt_status_string(rc) << ": " << rt_last_error(m) << std::endl;
+    rt_model_destroy(m);
+    if (rc != RT_OK) return false;
+    t = 0;
+    for (std::list<transition_data>::iterator it = container->data.begin(); it != container->data.end(); ++it, ++t) {
+        const size_t o = (size_t)t * L;
+        memcpy(it->lum_arr, &a[0][o], sizeof(double) * L);
+        memcpy(it->pump_eff_arr, &a[1][o], sizeof(double) * L);
+        memcpy(it->loss_rate_arr, &a[2][o], sizeof(double) * L);
+        memcpy(it->pump_rate_arr, &a[3][o], sizeof(double) * L);
+        memcpy(it->emiss_coeff_arr, &a[4][o], sizeof(double) * L);
+        it->lum = lum[t];
+    }
     return true;
 }
 

@@ -171,6 +171,36 @@ class Checker:
         assert rc == 0
         return out
 
+    LIM_KEYS = ("lum_arr", "pump_eff_arr", "loss_rate_arr", "pump_rate_arr", "emiss_coeff_arr", "exc_temp_arr")
+
+    def lim_luminosity(self, p, pop, up, low, beaming_factor=1.0, lay_nb_hg=None, layer0_intensity=True):
+        """lim_luminosity_lvg (maser_luminosity.cpp:7-106) + calc_exc_temp + calc_saturation_depth for listed transitions.
+        ref: the reference functions themselves (lay_nb_hg comes out of its own calc_gain; layer0_intensity is what the
+        reference does).  port: lay_nb_hg must be given (maser_postpass scalars[:, 4]) for the saturation part."""
+        d, s, hold = self._views(p)
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        up = np.ascontiguousarray(up, dtype=np.int32); low = np.ascontiguousarray(low, dtype=np.int32)
+        T = up.shape[0]
+        out = {k: np.zeros((T, p.L)) for k in self.LIM_KEYS}
+        out.update(lum=np.zeros(T), tau_sat=np.zeros(T), temp_sat=np.zeros(T), lay_nb_hg=np.zeros(T, dtype=np.int32))
+        arrs = [self.abi.dptr(out[k]) for k in self.LIM_KEYS]
+        if self.kind == "ref":
+            assert layer0_intensity
+            rc = self.lib.ref_lim_luminosity(C.byref(d), C.byref(s), self.abi.dptr(pop), T, self.abi.iptr(up), self.abi.iptr(low),
+                                             C.c_double(beaming_factor), *arrs, self.abi.dptr(out["lum"]),
+                                             self.abi.iptr(out["lay_nb_hg"]), self.abi.dptr(out["tau_sat"]),
+                                             self.abi.dptr(out["temp_sat"]))
+        else:
+            if lay_nb_hg is None:
+                lay_nb_hg = self.maser_postpass(p, pop, up, low)["scalars"][:, 4]
+            out["lay_nb_hg"][:] = np.asarray(lay_nb_hg, dtype=np.int32)
+            rc = self.lib.ora_lim_luminosity(C.byref(d), C.byref(s), self.abi.dptr(pop), T, self.abi.iptr(up), self.abi.iptr(low),
+                                             int(layer0_intensity), *arrs, self.abi.dptr(out["lum"]),
+                                             self.abi.iptr(out["lay_nb_hg"]), C.c_double(beaming_factor),
+                                             self.abi.dptr(out["tau_sat"]), self.abi.dptr(out["temp_sat"]))
+        assert rc == 0
+        return out
+
     def calc_molecular_populations(self, p, acceleration=None):
         """The warm-start chain + retry policy of calc_molecular_populations (radiative_transfer.cpp:219-289).
         ref: the reference function itself; port: ora_solve with RT_START_CHAINED."""

@@ -35,12 +35,16 @@
 #include "coll_rates_ch3oh.h"
 #include "coll_rates_oh.h"
 #include "coll_rates_h2o.h"
+#include "coll_rates_nh3.h"
+#include "coll_rates_h2co.h"
 #include "lvg_method_functions.h"
 #include "dust_model.h"
 #include "cloud_data.h"
 #include "iteration_lvg.h"
 #include "iteration_control.h"
 #include "transition_data.h"
+#include "maser_luminosity.h"
+#include <list>
 
 #include "../include/rt_b200.h"
 
@@ -123,6 +127,12 @@ struct synth_collisions : public collisional_transitions {
         case RT_RULE_H2O:
             reinterpret_cast<const h2o_collisions*>(this)->h2o_collisions::set_gas_param(tn, te, he, ph2, oh2, h, el, conc, ind);
             break;
+        case RT_RULE_NH3:
+            reinterpret_cast<const nh3_collisions*>(this)->nh3_collisions::set_gas_param(tn, te, he, ph2, oh2, h, el, conc, ind);
+            break;
+        case RT_RULE_H2CO:
+            reinterpret_cast<const h2co_collisions*>(this)->h2co_collisions::set_gas_param(tn, te, he, ph2, oh2, h, el, conc, ind);
+            break;
         default:
             // generic: base class fills indices (+ electron conc); neutral partner k gets, in order,
             // He, p-H2, o-H2, H (the convention every species class of the reference follows for its first tables)
@@ -145,6 +155,12 @@ struct synth_collisions : public collisional_transitions {
             break;
         case RT_RULE_H2O:
             reinterpret_cast<const h2o_collisions*>(this)->h2o_collisions::get_rate_neutrals(up, low, down, upr, tn, conc, ind);
+            break;
+        case RT_RULE_NH3:
+            reinterpret_cast<const nh3_collisions*>(this)->nh3_collisions::get_rate_neutrals(up, low, down, upr, tn, conc, ind);
+            break;
+        case RT_RULE_H2CO:
+            reinterpret_cast<const h2co_collisions*>(this)->h2co_collisions::get_rate_neutrals(up, low, down, upr, tn, conc, ind);
             break;
         default:
             collisional_transitions::get_rate_neutrals(up, low, down, upr, tn, conc, ind);
@@ -675,6 +691,53 @@ int ref_maser_postpass(const rt_model_desc* d, const rt_layer_soa* lay, const do
     return 0;
 }
 
+// lim_luminosity_lvg (maser_luminosity.cpp:7-106) + calc_saturation_depth (transition_data.cpp:456-483) of the
+// reference for listed transitions: the container is filled by transition_data_container::add (which also runs
+// calc_inv / calc_gain / calc_line_profile / calc_exc_temp), entries are matched back by their level numbers.
+// Per-layer outputs [nb_trans][L]; lum, tau_sat, temp_sat, lay_nb_hg [nb_trans].
+int ref_lim_luminosity(const rt_model_desc* d, const rt_layer_soa* lay, const double* pop, int nb_trans, const int* up, const int* low,
+                       double beaming_factor, double* lum_arr, double* pump_eff_arr, double* loss_rate_arr, double* pump_rate_arr,
+                       double* emiss_coeff_arr, double* exc_temp_arr, double* lum, int* lay_nb_hg, double* tau_sat, double* temp_sat)
+{
+    ref_ctx* c = build_ctx(d, lay);
+    null_buf nb;
+    cout_redirect quiet(&nb);
+    const int L = c->L;
+    std::vector<double> p(pop, pop + (size_t)L * c->N);
+    transition_data_container tc(c->cloud, c->diagram, c->einst);
+    // what transition_data_container::add does per transition (transition_data.cpp:441-451), without its de-duplication by
+    // quantum numbers (synthetic levels may share v, j, g) and without the final sort, so entry t stays transition t
+    for (int t = 0; t < nb_trans; t++) {
+        transition_data td(L, c->diagram->lev_array[low[t]], c->diagram->lev_array[up[t]]);
+        tc.calc_inv(td, p.data());
+        tc.calc_gain(td);
+        tc.calc_line_profile(td);
+        tc.calc_exc_temp(td, p.data());
+        tc.data.push_back(td);
+    }
+    lim_luminosity_lvg(c->scheme, &tc, c->cloud, c->diagram, c->einst, c->coll, p.data());
+    tc.calc_saturation_depth(beaming_factor);
+    int found = 0;
+    std::list<transition_data>::iterator it = tc.data.begin();
+    for (int t = 0; t < nb_trans && it != tc.data.end(); t++, ++it) {
+        if (it->trans->up_lev.nb != up[t] || it->trans->low_lev.nb != low[t]) break;
+        found++;
+        const size_t o = (size_t)t * L;
+        if (lum_arr) memcpy(lum_arr + o, it->lum_arr, sizeof(double) * L);
+        if (pump_eff_arr) memcpy(pump_eff_arr + o, it->pump_eff_arr, sizeof(double) * L);
+        if (loss_rate_arr) memcpy(loss_rate_arr + o, it->loss_rate_arr, sizeof(double) * L);
+        if (pump_rate_arr) memcpy(pump_rate_arr + o, it->pump_rate_arr, sizeof(double) * L);
+        if (emiss_coeff_arr) memcpy(emiss_coeff_arr + o, it->emiss_coeff_arr, sizeof(double) * L);
+        if (exc_temp_arr) memcpy(exc_temp_arr + o, it->exc_temp_arr, sizeof(double) * L);
+        if (lum) lum[t] = it->lum;
+        if (lay_nb_hg) lay_nb_hg[t] = it->lay_nb_hg;
+        if (tau_sat) tau_sat[t] = it->tau_sat;
+        if (temp_sat) temp_sat[t] = it->temp_sat;
+    }
+    delete c;
+    return found == nb_trans ? 0 : 1;
+}
+
 } // extern "C"
 
 // =========================================================================================================
@@ -835,6 +898,37 @@ int ref_adapter_scheme_solve(const rt_model_desc* d, const rt_layer_soa* lay, do
         : gpu_scheme_solve<rt_b200::iteration_scheme_lvg_gpu>(c, d, pop, start_mode, max_iter, min_err, accel, st, lay_begin, lay_end, device);
     delete c;
     return rc;
+}
+
+// lim_luminosity_lvg_gpu on the reference's container, then the reference's own calc_saturation_depth on the result
+int ref_adapter_lim_luminosity(const rt_model_desc* d, const rt_layer_soa* lay, const double* pop, int nb_trans, const int* up,
+                               const int* low, double beaming_factor, double* lum_arr, double* loss_rate_arr, double* pump_rate_arr,
+                               double* lum, double* tau_sat, int device)
+{
+    ref_ctx* c = build_ctx(d, lay);
+    null_buf nb;
+    cout_redirect quiet(&nb);
+    const int L = c->L;
+    std::vector<double> p(pop, pop + (size_t)L * c->N);
+    transition_data_container tc(c->cloud, c->diagram, c->einst);
+    for (int t = 0; t < nb_trans; t++) {
+        transition_data td(L, c->diagram->lev_array[low[t]], c->diagram->lev_array[up[t]]);
+        tc.calc_inv(td, p.data());
+        tc.calc_gain(td);
+        tc.calc_exc_temp(td, p.data());
+        tc.data.push_back(td);
+    }
+    const bool ok = rt_b200::lim_luminosity_lvg_gpu(c->scheme, &tc, c->cloud, c->diagram, c->einst, c->coll, p.data(), device, d->species_rule);
+    tc.calc_saturation_depth(beaming_factor);
+    int t = 0;
+    for (std::list<transition_data>::iterator it = tc.data.begin(); it != tc.data.end(); ++it, ++t) {
+        memcpy(lum_arr + (size_t)t * L, it->lum_arr, sizeof(double) * L);
+        memcpy(loss_rate_arr + (size_t)t * L, it->loss_rate_arr, sizeof(double) * L);
+        memcpy(pump_rate_arr + (size_t)t * L, it->pump_rate_arr, sizeof(double) * L);
+        lum[t] = it->lum; tau_sat[t] = it->tau_sat;
+    }
+    delete c;
+    return ok ? 0 : 1;
 }
 
 int ref_adapter_scheme_probe(const rt_model_desc* d, const rt_layer_soa* lay, int l, const double* pop, double* matrix, double* df,

@@ -279,7 +279,11 @@ static void set_gas_param(const ora_model* m, ora_layer* s, double tn, double te
     switch (m->d->species_rule) {
     case RT_RULE_CH3OH:
     case RT_RULE_OH_HF:
+    case RT_RULE_H2CO: /* coll_rates_h2co.cpp:160-168 */
         s->conc[0] = he; s->conc[1] = ph2; s->conc[2] = oh2;
+        break;
+    case RT_RULE_NH3: /* coll_rates_nh3.cpp:261-271 */
+        s->conc[0] = he; s->conc[1] = ph2; s->conc[2] = oh2; s->conc[3] = h;
         break;
     case RT_RULE_H2O:
         s->conc[0] = he; s->conc[1] = he + 0.2 * h; s->conc[2] = ph2; s->conc[3] = oh2; s->conc[4] = ph2 + oh2; s->conc[5] = h;
@@ -343,6 +347,17 @@ static void rate_neutrals(const ora_model* m, const ora_layer* s, int up, int lo
                  + tab_rate(&T[3], up, low, s->idx[3], tn) * s->conc[3] + tab_rate(&T[5], up, low, s->idx[5], tn) * s->conc[5];
         else
             dn = tab_rate(&T[1], up, low, s->idx[1], tn) * s->conc[1] + tab_rate(&T[4], up, low, s->idx[4], tn) * s->conc[4];
+        break;
+    case RT_RULE_NH3: /* coll_rates_nh3.cpp:273-290 */
+        if (up < T[0].nb_lev) dn = tab_rate(&T[0], up, low, s->idx[0], tn) * s->conc[0];
+        if (up < T[1].nb_lev)
+            dn += tab_rate(&T[1], up, low, s->idx[1], tn) * s->conc[1] + tab_rate(&T[2], up, low, s->idx[2], tn) * s->conc[2]
+                  + tab_rate(&T[3], up, low, s->idx[3], tn) * s->conc[3];
+        break;
+    case RT_RULE_H2CO: /* coll_rates_h2co.cpp:170-185 */
+        if (up < T[0].nb_lev) dn = tab_rate(&T[0], up, low, s->idx[0], tn) * s->conc[0];
+        if (up < T[1].nb_lev)
+            dn += tab_rate(&T[1], up, low, s->idx[1], tn) * s->conc[1] + tab_rate(&T[2], up, low, s->idx[2], tn) * s->conc[2];
         break;
     default:
         for (int k = 0; k < m->nb1; k++)
@@ -1046,6 +1061,95 @@ int ora_maser_postpass(const rt_model_desc* d, const rt_layer_soa* lay, const do
         if (scalars) { double* s = scalars + 5 * (size_t)t; s[0] = inv; s[1] = gain; s[2] = tau_eff; s[4] = hg; }
     }
     free(inv_l); free(gain_l); free(line_opacity); free(dust_opacity); free(vel_width); free(depth);
+    model_destroy(m);
+    return 0;
+}
+
+/* lim_luminosity_lvg (maser_luminosity.cpp:7-106), calc_exc_temp (transition_data.cpp:225-237) and
+ * calc_saturation_depth (transition_data.cpp:456-483) for listed transitions.  Per-layer outputs [nb_trans][L].
+ * layer0_intensity != 0: the reference's literal behaviour -- intensity_calc receives the base pointer of the population
+ * array (maser_luminosity.cpp:54,58), i.e. J of the loss terms is evaluated with the populations of layer 0.
+ * lay_nb_hg [nb_trans]: input (layer of the highest gain from ora_maser_postpass), NULL skips the saturation part. */
+int ora_lim_luminosity(const rt_model_desc* d, const rt_layer_soa* lay, const double* pop, int nb_trans, const int* up, const int* low,
+                       int layer0_intensity, double* lum_arr, double* pump_eff_arr, double* loss_rate_arr, double* pump_rate_arr,
+                       double* emiss_coeff_arr, double* exc_temp_arr, double* lum, const int* lay_nb_hg, double beaming_factor,
+                       double* tau_sat, double* temp_sat)
+{
+    ora_model* m = model_create(d);
+    const int N = m->N, L = lay->nb_lay;
+    const rt_params* pr = &d->params;
+    double* up_loss = (double*)malloc(sizeof(double) * L);
+    double* low_loss = (double*)malloc(sizeof(double) * L);
+    for (int t = 0; t < nb_trans; t++) {
+        const int lo = low[t], hi = up[t];
+        const double gu = d->g[hi], gl = d->g[lo];
+        const double energy = d->energy[hi] - d->energy[lo];
+        double lum_t = 0.;
+        for (int l = 0; l < L; l++) {
+            const double* pl = pop + (size_t)l * N;
+            const double* pj = layer0_intensity ? pop : pl;
+            ora_layer s;
+            layer_set(m, lay, l, &s);
+            for (int k = 0; k <= 1; k++) {
+                const int j = k == 0 ? lo : hi;
+                double loss = 0.;
+                for (int i = 0; i < N; i++) {
+                    const double Aij = d->einst[(size_t)i * N + j], Aji = d->einst[(size_t)j * N + i];
+                    if (Aij != 0. && i != lo && i != hi) {
+                        if (i < j && pl[i] * Aij > pl[j] * Aji) loss += Aji * (1. + intensity_any(m, &s, j, i, pj));
+                        else if (i > j && pl[i] * Aij < pl[j] * Aji) loss += Aji * intensity_any(m, &s, i, j, pj);
+                    }
+                }
+                if (k == 0) low_loss[l] = loss;
+                else up_loss[l] = loss;
+            }
+            for (int i = 0; i < N; i++) { /* get_rate_neutrals(init, fin), coll_rates.cpp:225-240 */
+                double dn, ur;
+                if (i != lo) {
+                    if (lo > i) { rate_neutrals(m, &s, lo, i, &dn, &ur); low_loss[l] += dn; }
+                    else { rate_neutrals(m, &s, i, lo, &dn, &ur); low_loss[l] += ur; }
+                }
+                if (i != hi) {
+                    if (hi > i) { rate_neutrals(m, &s, hi, i, &dn, &ur); up_loss[l] += dn; }
+                    else { rate_neutrals(m, &s, i, hi, &dn, &ur); up_loss[l] += ur; }
+                }
+            }
+            const size_t o = (size_t)t * L + l;
+            const double h2 = lay->ph2_conc[l] + lay->oh2_conc[l];
+            const double inversion = pl[hi] / gu - pl[lo] / gl;
+            double lum_l, eff_l;
+            if (inversion > 0.) {
+                lum_l = inversion / (1. / (up_loss[l] * gu) + 1. / (low_loss[l] * gl)) * lay->mol_conc[l];
+                eff_l = inversion / (pl[hi] / gu + pl[lo] / gl);
+            }
+            else lum_l = eff_l = 1.e-99;
+            lum_t += lum_l * lay->dz[l];
+            if (lum_arr) lum_arr[o] = lum_l;
+            if (pump_eff_arr) pump_eff_arr[o] = eff_l;
+            if (emiss_coeff_arr) emiss_coeff_arr[o] = h2 * lay->mol_conc[l] / lay->velg_n[l];
+            if (loss_rate_arr) loss_rate_arr[o] = (up_loss[l] * gu + low_loss[l] * gl) / (gu + gl);
+            if (pump_rate_arr) pump_rate_arr[o] = 0.5 * (pl[hi] * up_loss[l] + pl[lo] * low_loss[l]) / h2;
+            if (exc_temp_arr) exc_temp_arr[o] = pr->cm_inverse_to_kelvins * energy / log((pl[lo] * gu) / (pl[hi] * gl));
+        }
+        if (lum) lum[t] = lum_t / lay->height;
+        if (lay_nb_hg && (tau_sat || temp_sat)) {
+            const int l = lay_nb_hg[t];
+            const double* pl = pop + (size_t)l * N;
+            const double exc_temp = pr->cm_inverse_to_kelvins * energy / log((pl[lo] * gu) / (pl[hi] * gl));
+            double ts = 0., tmp = 0.;
+            if (exc_temp < 0.) {
+                const double source_function = 1. / (1. - exp(energy * pr->cm_inverse_to_kelvins / exc_temp));
+                const double cmb_intensity = 1. / (exp(energy * pr->cm_inverse_to_kelvins / 2.73) - 1.);
+                const double intensity_0 = source_function + cmb_intensity;
+                const double loss = (up_loss[l] * gu + low_loss[l] * gl) / (gu + gl);
+                ts = log(loss / (d->einst[(size_t)hi * N + lo] * beaming_factor * intensity_0));
+                tmp = intensity_0 * exp(ts) * pr->planck_constant * (pr->speed_of_light * energy) / pr->boltzmann_constant;
+            }
+            if (tau_sat) tau_sat[t] = ts;
+            if (temp_sat) temp_sat[t] = tmp;
+        }
+    }
+    free(up_loss); free(low_loss);
     model_destroy(m);
     return 0;
 }

@@ -14,7 +14,7 @@ from typing import List, Optional
 import numpy as np
 
 RT_OK = 0
-RT_RULE_GENERIC, RT_RULE_CH3OH, RT_RULE_OH_HF, RT_RULE_H2O = 0, 1, 2, 3
+RT_RULE_GENERIC, RT_RULE_CH3OH, RT_RULE_OH_HF, RT_RULE_H2O, RT_RULE_NH3, RT_RULE_H2CO = 0, 1, 2, 3, 4, 5
 RT_SCHEME_LVG, RT_SCHEME_LINE_OVERLAP = 0, 1
 RT_START_GIVEN, RT_START_BOUNDARY, RT_START_LTE, RT_START_CHAINED = 0, 1, 2, 3
 
@@ -28,7 +28,7 @@ class rt_params(C.Structure):
         ("max_dx", C.c_double),
         ("accel_start", C.c_int), ("accel_period", C.c_int), ("nb_prev_steps", C.c_int), ("reserved0", C.c_int),
         ("boltzmann_constant", C.c_double), ("cm_inverse_to_kelvins", C.c_double), ("speed_of_light", C.c_double),
-        ("eight_pi", C.c_double), ("onedivby_sqrt_pi", C.c_double),
+        ("eight_pi", C.c_double), ("onedivby_sqrt_pi", C.c_double), ("planck_constant", C.c_double),
     ]
 
 
@@ -94,6 +94,7 @@ def default_params() -> rt_params:
     p.speed_of_light = 2.99792458e+10
     p.eight_pi = 25.132741228718345
     p.onedivby_sqrt_pi = 0.56418958354775629
+    p.planck_constant = 6.62607004e-27
     return p
 
 

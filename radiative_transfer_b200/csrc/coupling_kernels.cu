@@ -48,6 +48,17 @@ __device__ __forceinline__ void rate_neutrals(const DevModel& d, int lay, int up
         else
             dn = tab_rate(T[1], up, low, idx[1], tn) * conc[1] + tab_rate(T[4], up, low, idx[4], tn) * conc[4];
         break;
+    case RT_RULE_NH3: // coll_rates_nh3.cpp:273-290: the three hydrogen tables share the level limit of table 1
+        if (up < T[0].nb_lev) dn = tab_rate(T[0], up, low, idx[0], tn) * conc[0];
+        if (up < T[1].nb_lev)
+            dn += tab_rate(T[1], up, low, idx[1], tn) * conc[1] + tab_rate(T[2], up, low, idx[2], tn) * conc[2]
+                  + tab_rate(T[3], up, low, idx[3], tn) * conc[3];
+        break;
+    case RT_RULE_H2CO: // coll_rates_h2co.cpp:170-185
+        if (up < T[0].nb_lev) dn = tab_rate(T[0], up, low, idx[0], tn) * conc[0];
+        if (up < T[1].nb_lev)
+            dn += tab_rate(T[1], up, low, idx[1], tn) * conc[1] + tab_rate(T[2], up, low, idx[2], tn) * conc[2];
+        break;
     default: // coll_rates.cpp:181-197
         for (int k = 0; k < d.nb1; k++)
             if (up < T[k].nb_lev) dn += tab_rate(T[k], up, low, idx[k], tn) * conc[k];
@@ -148,15 +159,9 @@ void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int half
 // hyperfine lines); writes the two radiative rates of each line
 //     yd = A_ul (1 + J)   (u -> l),   yu = A_lu J   (l -> u)          iteration_lvg.cpp:137-144
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_intensity(DevModel d, int nlay_bound)
+__device__ __forceinline__ void intensity_group(const DevModel& d, int lay, int gi, const double* __restrict__ pop)
 {
-    const int a = blockIdx.y;
-    if (a >= nlay_bound || a >= *d.n_active) return;
-    const int lay = d.active[a];
-    const int gi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gi >= d.G) return;
     const LayerCtx c = dev_layer_ctx(d, lay);
-    const double* __restrict__ pop = d.pop + (size_t)lay * d.N;
     const int nb = d.grp[3 * gi], la = d.grp[3 * gi + 1];
     const int u1 = d.tr_u[la], l1 = d.tr_l[la];
     const double A1ul = d.tr_Aul[la], A1lu = d.tr_Alu[la];
@@ -181,12 +186,102 @@ __global__ void __launch_bounds__(128) k_intensity(DevModel d, int nlay_bound)
     }
 }
 
+__global__ void __launch_bounds__(128) k_intensity(DevModel d, int nlay_bound)
+{
+    const int a = blockIdx.y;
+    if (a >= nlay_bound || a >= *d.n_active) return;
+    const int lay = d.active[a];
+    const int gi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gi >= d.G) return;
+    intensity_group(d, lay, gi, d.pop + (size_t)lay * d.N);
+}
+
+// every layer (no active list), populations from pop + lay * pop_stride (stride 0: the same vector for all layers)
+__global__ void __launch_bounds__(128) k_intensity_all(DevModel d, const double* __restrict__ pop, size_t pop_stride)
+{
+    const int lay = blockIdx.y;
+    const int gi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gi >= d.G) return;
+    intensity_group(d, lay, gi, pop + (size_t)lay * pop_stride);
+}
+
 void launch_intensity(const DevModel& d, cudaStream_t s, int nlay_bound)
 {
     if (d.G == 0) return;
     dim3 grid((d.G + 127) / 128, nlay_bound);
     g_rt_launches++;
     k_intensity<<<grid, 128, 0, s>>>(d, nlay_bound);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K6: loss rates of the two levels of listed transitions, lim_luminosity_lvg
+// (maser_luminosity.cpp:44-76).  One CTA per (layer, transition); threads stride over the partner level i:
+//   radiative: every A_ij != 0 with i outside the transition and no inversion between i and j (tested with the
+//   populations of the CURRENT layer) contributes the out-of-j rate A_ji (1 + J) (i < j) or A_ji J (i > j); the rates
+//   are the yd / yu of k_intensity_all (J from the populations the host chose); a pair with A != 0 that is not a line
+//   of the scheme (hyperfine doublets of the overlap scheme, iteration_lvg.cpp:503-526) has J = 0;
+//   collisional: sum over i != j of get_rate_neutrals(j -> i) (coll_rates.cpp:225-240), neutrals only.
+// out [T][L][2] = {low_loss_rate, up_loss_rate}.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_loss_rates(DevModel d, const double* __restrict__ pop, int nb_trans, const int* __restrict__ up,
+                                                    const int* __restrict__ low, double* __restrict__ out)
+{
+    const int lay = blockIdx.x, t = blockIdx.y;
+    const int N = d.N, lo = low[t], hi = up[t];
+    const double* __restrict__ p = pop + (size_t)lay * N;
+    const double* __restrict__ yd = d.yd + (size_t)lay * d.R;
+    const double* __restrict__ yu = d.yu + (size_t)lay * d.R;
+    double acc[2] = {0., 0.};
+    for (int i = threadIdx.x; i < N; i += blockDim.x) {
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            const int j = k == 0 ? lo : hi;
+            if (i == j) continue;
+            const double Aij = d.einst[(size_t)i * N + j], Aji = d.einst[(size_t)j * N + i];
+            if (Aij != 0. && i != lo && i != hi) {
+                const bool down = i < j && p[i] * Aij > p[j] * Aji;
+                const bool upw = i > j && p[i] * Aij < p[j] * Aji;
+                if (down || upw) {
+                    double rate = down ? Aji : 0.; // J = 0 when the pair is not a line of the scheme
+                    for (int e = d.row_ptr[j]; e < d.row_ptr[j + 1]; e++)
+                        if (d.row_col[e] == i) {
+                            const int ln = d.row_line[e];
+                            rate = (ln & 1) ? yu[ln >> 1] : yd[ln >> 1]; // the out-of-row rate, as in k_assemble
+                            break;
+                        }
+                    acc[k] += rate;
+                }
+            }
+            double dn, ur;
+            if (j > i) { rate_neutrals(d, lay, j, i, dn, ur); acc[k] += dn; }
+            else { rate_neutrals(d, lay, i, j, dn, ur); acc[k] += ur; }
+        }
+    }
+    __shared__ double red[2][4];
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+        if ((threadIdx.x & 31) == 0) red[k][threadIdx.x >> 5] = acc[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        const int k = threadIdx.x;
+        out[((size_t)t * d.L + lay) * 2 + k] = red[k][0] + red[k][1] + red[k][2] + red[k][3];
+    }
+}
+
+void launch_loss_rates(const DevModel& d, cudaStream_t s, const double* pop_dev, const double* pop_intensity, size_t intensity_stride,
+                       int nb_trans, const int* up_dev, const int* low_dev, double* out_dev)
+{
+    if (d.G > 0) {
+        dim3 gi((d.G + 127) / 128, d.L);
+        g_rt_launches++;
+        k_intensity_all<<<gi, 128, 0, s>>>(d, pop_intensity, intensity_stride);
+    }
+    dim3 grid(d.L, nb_trans);
+    g_rt_launches++;
+    k_loss_rates<<<grid, 128, 0, s>>>(d, pop_dev, nb_trans, up_dev, low_dev, out_dev);
 }
 
 // ------------------------------------------------------------------------------------------------------------

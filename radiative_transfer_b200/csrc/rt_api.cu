@@ -75,6 +75,7 @@ void rt_params_default(rt_params* p)
     p->speed_of_light = 2.99792458e+10;
     p->eight_pi = 25.132741228718345;
     p->onedivby_sqrt_pi = 0.56418958354775629;
+    p->planck_constant = 6.62607004e-27;
 }
 
 const char* rt_status_string(rt_status s)
@@ -168,6 +169,8 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
     if (desc->params.nb_prev_steps != 5) { g_create_error = "only nb_prev_steps == 5 is implemented"; return RT_ERR_UNSUPPORTED; }
     if (desc->scheme == RT_SCHEME_LINE_OVERLAP && (!desc->overlap1 || !desc->overlap2)) { g_create_error = "overlap tables missing"; return RT_ERR_INVALID; }
     if ((desc->species_rule == RT_RULE_CH3OH || desc->species_rule == RT_RULE_OH_HF) && desc->nb_neutral_tables < 3) { g_create_error = "rule needs 3 neutral tables"; return RT_ERR_INVALID; }
+    if (desc->species_rule == RT_RULE_H2CO && desc->nb_neutral_tables < 3) { g_create_error = "rule needs 3 neutral tables"; return RT_ERR_INVALID; }
+    if (desc->species_rule == RT_RULE_NH3 && desc->nb_neutral_tables < 4) { g_create_error = "NH3 rule needs 4 neutral tables"; return RT_ERR_INVALID; }
     if (desc->species_rule == RT_RULE_H2O && desc->nb_neutral_tables < 6) { g_create_error = "H2O rule needs 6 neutral tables"; return RT_ERR_INVALID; }
 
     int ndev = 0;
@@ -206,6 +209,7 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
     d.jq = dev_upload(m, jq.data(), N, false);
     d.einst = dev_upload(m, desc->einst, (size_t)N * N, false);
     m->h_energy.assign(desc->energy, desc->energy + N);
+    m->h_g.assign(desc->g, desc->g + N);
     m->h_einst.assign(desc->einst, desc->einst + (size_t)N * N);
 
     // ---- lines and groups ---------------------------------------------------------------------------------
@@ -449,7 +453,8 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
         }
         const double he = lay->he_conc[l], ph2 = lay->ph2_conc[l], oh2 = lay->oh2_conc[l], h = lay->h_conc[l];
         switch (d.rule) {
-        case RT_RULE_CH3OH: case RT_RULE_OH_HF: c[0] = he; c[1] = ph2; c[2] = oh2; break;
+        case RT_RULE_CH3OH: case RT_RULE_OH_HF: case RT_RULE_H2CO: c[0] = he; c[1] = ph2; c[2] = oh2; break;
+        case RT_RULE_NH3: c[0] = he; c[1] = ph2; c[2] = oh2; c[3] = h; break; // coll_rates_nh3.cpp:261-271
         case RT_RULE_H2O: c[0] = he; c[1] = he + 0.2 * h; c[2] = ph2; c[3] = oh2; c[4] = ph2 + oh2; c[5] = h; break;
         default: { const double cc[4] = {he, ph2, oh2, h}; for (int k = 0; k < d.nb1; k++) c[k] = cc[k < 4 ? k : 3]; }
         }
@@ -466,6 +471,10 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
     m->h_vel_n.assign(lay->vel_n ? lay->vel_n : lay->temp_n, (lay->vel_n ? lay->vel_n : lay->temp_n) + L);
     m->h_height = lay->height;
     m->h_vel_turb.assign(lay->vel_turb, lay->vel_turb + L);
+    m->h_h2_conc.resize(L);
+    for (int l = 0; l < L; l++) m->h_h2_conc[l] = lay->ph2_conc[l] + lay->oh2_conc[l]; // maser_luminosity.cpp:79,95
+    m->h_mol_conc.assign(lay->mol_conc, lay->mol_conc + L);
+    m->h_velg.assign(lay->velg_n, lay->velg_n + L);
 
     const size_t mat = (size_t)L * Np * Np;
     d.Cmat = dev_alloc<double>(m, mat, true, false);
@@ -968,5 +977,92 @@ extern "C" rt_status rt_maser_postpass(rt_model* m, const double* pop, int nb_tr
     }
     for (void* p : tmp) cudaFree(p);
     CK(e);
+    return RT_OK;
+}
+
+// ---- rt_lim_luminosity -------------------------------------------------------------------
+void launch_loss_rates(const DevModel& d, cudaStream_t s, const double* pop_dev, const double* pop_intensity, size_t intensity_stride,
+                       int nb_trans, const int* up_dev, const int* low_dev, double* out_dev);
+
+extern "C" rt_status rt_lim_luminosity(rt_model* m, const double* pop, int nb_trans, const int* up, const int* low,
+                                       int layer0_intensity, double* lum_arr, double* pump_eff_arr, double* loss_rate_arr,
+                                       double* pump_rate_arr, double* emiss_coeff_arr, double* exc_temp_arr, double* lum,
+                                       const int* lay_nb_hg, double beaming_factor, double* tau_sat, double* temp_sat)
+{
+    NEED_CLOUD();
+    const DevModel& d = m->d;
+    const int L = d.L, N = d.N;
+    if (!pop || nb_trans < 0 || (nb_trans > 0 && (!up || !low))) return RT_ERR_INVALID;
+    if (nb_trans == 0) return RT_OK;
+    for (int t = 0; t < nb_trans; t++)
+        if (low[t] < 0 || up[t] >= N || up[t] <= low[t]) { m->last_error = "transition must have up > low"; return RT_ERR_INVALID; }
+    rt_status r = rt_set_populations(m, pop);
+    if (r != RT_OK) return r;
+    int *up_dev = nullptr, *low_dev = nullptr;
+    double* out_dev = nullptr;
+    const size_t nout = (size_t)nb_trans * L * 2;
+    CK(cudaMalloc(&up_dev, sizeof(int) * nb_trans));
+    CK(cudaMalloc(&low_dev, sizeof(int) * nb_trans));
+    CK(cudaMalloc(&out_dev, sizeof(double) * nout));
+    CK(cudaMemcpy(up_dev, up, sizeof(int) * nb_trans, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(low_dev, low, sizeof(int) * nb_trans, cudaMemcpyHostToDevice));
+    const int c_l = rt_prof_class(m, "loss_rates");
+    m->prof_layers = L;
+    rt_prof_begin(m, c_l, m->stream, 0., 0.);
+    launch_loss_rates(d, m->stream, d.pop, d.pop, layer0_intensity ? 0 : (size_t)N, nb_trans, up_dev, low_dev, out_dev);
+    rt_prof_end(m, c_l, m->stream);
+    CK(cudaStreamSynchronize(m->stream));
+    CK(cudaGetLastError());
+    std::vector<double> rates(nout);
+    CK(cudaMemcpy(rates.data(), out_dev, sizeof(double) * nout, cudaMemcpyDeviceToHost));
+    cudaFree(up_dev); cudaFree(low_dev); cudaFree(out_dev);
+
+    // the scalar part in the reference's own expression order (maser_luminosity.cpp:78-101)
+    const rt_params& pr = d.prm;
+    for (int t = 0; t < nb_trans; t++) {
+        const int u = up[t], lo = low[t];
+        const double gu = m->h_g[u], gl = m->h_g[lo];
+        const double energy = m->h_energy[u] - m->h_energy[lo];
+        double lum_t = 0.;
+        for (int l = 0; l < L; l++) {
+            const size_t o = (size_t)t * L + l;
+            const double low_loss = rates[2 * o], up_loss = rates[2 * o + 1];
+            const double pu = pop[(size_t)l * N + u], pl = pop[(size_t)l * N + lo];
+            const double inversion = pu / gu - pl / gl;
+            double lum_l, eff_l;
+            if (inversion > 0.) {
+                lum_l = inversion / (1. / (up_loss * gu) + 1. / (low_loss * gl)) * m->h_mol_conc[l];
+                eff_l = inversion / (pu / gu + pl / gl);
+            }
+            else lum_l = eff_l = 1.e-99;
+            lum_t += lum_l * m->h_dz[l];
+            if (lum_arr) lum_arr[o] = lum_l;
+            if (pump_eff_arr) pump_eff_arr[o] = eff_l;
+            if (emiss_coeff_arr) emiss_coeff_arr[o] = m->h_h2_conc[l] * m->h_mol_conc[l] / m->h_velg[l];
+            if (loss_rate_arr) loss_rate_arr[o] = (up_loss * gu + low_loss * gl) / (gu + gl);
+            if (pump_rate_arr) pump_rate_arr[o] = 0.5 * (pu * up_loss + pl * low_loss) / m->h_h2_conc[l];
+            if (exc_temp_arr) exc_temp_arr[o] = pr.cm_inverse_to_kelvins * energy / log((pl * gu) / (pu * gl)); // transition_data.cpp:234
+        }
+        if (lum) lum[t] = lum_t / m->h_height;
+        if (lay_nb_hg && (tau_sat || temp_sat)) { // transition_data.cpp:456-483
+            const int l = lay_nb_hg[t];
+            double ts = 0., tmp = 0.;
+            if (l >= 0 && l < L) {
+                const size_t o = (size_t)t * L + l;
+                const double pu = pop[(size_t)l * N + u], pl = pop[(size_t)l * N + lo];
+                const double exc_temp = pr.cm_inverse_to_kelvins * energy / log((pl * gu) / (pu * gl));
+                if (exc_temp < 0.) {
+                    const double source_function = 1. / (1. - exp(energy * pr.cm_inverse_to_kelvins / exc_temp));
+                    const double cmb_intensity = 1. / (exp(energy * pr.cm_inverse_to_kelvins / 2.73) - 1.);
+                    const double intensity_0 = source_function + cmb_intensity;
+                    const double loss = (rates[2 * o + 1] * gu + rates[2 * o] * gl) / (gu + gl);
+                    ts = log(loss / (m->h_einst[(size_t)u * N + lo] * beaming_factor * intensity_0));
+                    tmp = intensity_0 * exp(ts) * pr.planck_constant * (pr.speed_of_light * energy) / pr.boltzmann_constant;
+                }
+            }
+            if (tau_sat) tau_sat[t] = ts;
+            if (temp_sat) temp_sat[t] = tmp;
+        }
+    }
     return RT_OK;
 }

@@ -90,6 +90,8 @@ struct rt_model {
     std::vector<int> h_tr_u, h_tr_l, h_grp;
     std::vector<rt_layer_status> h_status;
     std::vector<double> h_dz, h_vel_n, h_vel_turb;
+    std::vector<double> h_h2_conc, h_mol_conc, h_velg; // rt_lim_luminosity: ph2 + oh2, mol_conc, dv/dz per layer
+    std::vector<int> h_g;
     double h_height = 0.;
     long long iters_enqueued = 0;
     std::vector<std::vector<double>> h_dust_en, h_dust_abs;

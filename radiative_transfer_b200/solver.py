@@ -26,6 +26,7 @@ ENTRY_POINTS = [
     "rt_calc_molecular_populations", "rt_solve_device", "rt_get_status", "rt_get_populations", "rt_set_populations",
     "rt_profile_reset", "rt_profile_get", "rt_iterations_enqueued", "rt_maser_postpass", "rt_cloud_rebuild",
     "rt_profile_get_work", "rt_launch_count", "rt_timer_begin", "rt_timer_end", "rt_device_fp64_peak",
+    "rt_lim_luminosity",
 ]
 
 
@@ -183,6 +184,25 @@ class Model:
                                            C.c_double(delta_aspect), C.c_double(velocity_shift), abi.dptr(out["inv"]),
                                            abi.dptr(out["gain"]), abi.dptr(out["scalars"]), abi.dptr(out["tau_vs_aspect"]),
                                            abi.dptr(out["tau_vs_freq"])), "rt_maser_postpass")
+        return out
+
+    # -- lim_luminosity_lvg + calc_exc_temp + calc_saturation_depth (maser_luminosity.cpp:7-106, transition_data.cpp) ---
+    LIM_KEYS = ("lum_arr", "pump_eff_arr", "loss_rate_arr", "pump_rate_arr", "emiss_coeff_arr", "exc_temp_arr")
+
+    def lim_luminosity(self, pop, up, low, beaming_factor=1.0, lay_nb_hg=None, layer0_intensity=True):
+        """Pump / loss rates and limiting luminosity of listed transitions.  layer0_intensity=True is the reference's
+        literal behaviour (J of the loss terms from the populations of layer 0); lay_nb_hg (maser_postpass
+        scalars[:, 4]) switches the saturation depth on."""
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        up = np.ascontiguousarray(up, dtype=np.int32); low = np.ascontiguousarray(low, dtype=np.int32)
+        T = up.shape[0]
+        out = {k: np.zeros((T, self.L)) for k in self.LIM_KEYS}
+        out.update(lum=np.zeros(T), tau_sat=np.zeros(T), temp_sat=np.zeros(T))
+        hg = None if lay_nb_hg is None else np.ascontiguousarray(lay_nb_hg, dtype=np.int32)
+        self._ck(self.L_.rt_lim_luminosity(self.h, abi.dptr(pop), T, abi.iptr(up), abi.iptr(low), int(layer0_intensity),
+                                           *[abi.dptr(out[k]) for k in self.LIM_KEYS], abi.dptr(out["lum"]),
+                                           abi.iptr(hg) if hg is not None else None, C.c_double(beaming_factor),
+                                           abi.dptr(out["tau_sat"]), abi.dptr(out["temp_sat"])), "rt_lim_luminosity")
         return out
 
     # -- instrumentation --------------------------------------------------------------------------------------

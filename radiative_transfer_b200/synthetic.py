@@ -13,8 +13,8 @@ from __future__ import annotations
 
 import numpy as np
 
-from .abi import (CollTable, DustComp, OverlapTable, Problem, RT_RULE_CH3OH, RT_RULE_GENERIC, RT_RULE_H2O,
-                  RT_RULE_OH_HF, RT_SCHEME_LINE_OVERLAP, RT_SCHEME_LVG, RT_START_BOUNDARY, RT_START_LTE)
+from .abi import (CollTable, DustComp, OverlapTable, Problem, RT_RULE_CH3OH, RT_RULE_GENERIC, RT_RULE_H2CO,
+                  RT_RULE_H2O, RT_RULE_NH3, RT_RULE_OH_HF, RT_SCHEME_LINE_OVERLAP, RT_SCHEME_LVG, RT_START_BOUNDARY, RT_START_LTE)
 
 AMU = 1.660539040e-24
 
@@ -329,6 +329,33 @@ def config_h2o(L: int = 200, N: int = 411, seed: int = 20240004) -> Problem:
                    cloud_kw=dict(x_mol=3e-5, t_hi=1200.0))
 
 
+def config_nh3(L: int = 50, seed: int = 20240006) -> Problem:
+    """NH3-like molecule (N = 42): 4 neutral tables He / p-H2 / o-H2 / H mixed by
+    nh3_collisions::get_rate_neutrals (coll_rates_nh3.cpp:273-290): the three hydrogen tables share the level limit of the
+    p-H2 table, which the tables below make visible (He covers fewer levels, o-H2 and H more)."""
+    rng = np.random.default_rng(seed)
+    mol = make_ch3oh(rng, 1, 6, 7)
+    N = len(mol["energy"])
+    tg = lambda n, hi: np.concatenate([[0.0], np.linspace(15.0, hi, n - 1)])
+    b = mol["base"]
+    tabs = [_coll_table(rng, N - 10, tg(16, 300.0), b * 0.5), _coll_table(rng, N - 4, tg(12, 200.0), b),
+            _coll_table(rng, N, tg(12, 200.0), b * 1.3), _coll_table(rng, N, tg(9, 500.0), b * 0.8)]
+    return _finish("nh3_para", "pNH3", RT_RULE_NH3, RT_SCHEME_LVG, mol, tabs, 4, rng, L, 1, True, 150, RT_START_BOUNDARY)
+
+
+def config_h2co(L: int = 50, seed: int = 20240007) -> Problem:
+    """H2CO-like molecule (N = 40): 3 neutral tables He / p-H2 / o-H2, h2co_collisions::get_rate_neutrals
+    (coll_rates_h2co.cpp:170-185)."""
+    rng = np.random.default_rng(seed)
+    mol = make_ch3oh(rng, 1, 5, 8)
+    N = len(mol["energy"])
+    tg = lambda n, hi: np.concatenate([[0.0], np.linspace(10.0, hi, n - 1)])
+    b = mol["base"]
+    tabs = [_coll_table(rng, N - 8, tg(14, 300.0), b * 0.5), _coll_table(rng, N - 2, tg(11, 300.0), b),
+            _coll_table(rng, N, tg(11, 300.0), b * 1.4)]
+    return _finish("h2co_ortho", "oH2CO", RT_RULE_H2CO, RT_SCHEME_LVG, mol, tabs, 3, rng, L, 1, True, 150, RT_START_BOUNDARY)
+
+
 def config_sweep_point(i_n: int, i_t: int, i_c: int, grid: int = 8, L: int = 200, seed: int = 20240002, **kw) -> Problem:
     """Config 5: one point of the density x temperature x specific-column-density grid (same molecule as config 2;
     n_H2 in logspace(4,8), T in linspace(30,300), n_mol/|dv/dz| in logspace): only the cloud changes."""
@@ -350,6 +377,10 @@ def small(name: str, L: int = 6) -> Problem:
         return config_ch3oh(L=L, n_vt=3, n_k=8, n_j=10)  # N = 240
     if name == "h2o_small":
         return config_h2o(L=L, N=150)
+    if name == "nh3":
+        return config_nh3(L=L)
+    if name == "h2co":
+        return config_h2co(L=L)
     if name == "generic":
         p = config_ch3oh(L=L, n_vt=1, n_k=5, n_j=6)  # N = 30
         p.species_rule = RT_RULE_GENERIC

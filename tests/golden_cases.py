@@ -15,6 +15,8 @@ CASES = {  # name -> (synthetic.small name, layers)
     "oh_overlap": ("oh_overlap", 3),
     "ch3oh_small": ("ch3oh_small", 3),
     "h2o_small": ("h2o_small", 2),
+    "nh3": ("nh3", 3),     # nh3_collisions / h2co_collisions mixing rules
+    "h2co": ("h2co", 3),
 }
 
 
@@ -102,6 +104,10 @@ def compute(chk, p):
     post = chk.maser_postpass(p, b, up, low)
     for k, v in post.items():
         out["post_" + k] = v
+    # pump / loss rates, limiting luminosity, saturation depth (lim_luminosity_lvg, calc_saturation_depth) on the same input
+    lim = chk.lim_luminosity(p, b, up, low, beaming_factor=1.0, lay_nb_hg=post["scalars"][:, 4])
+    for k, v in lim.items():
+        out["lim_" + k] = v
     cp, cst, _ = chk.calc_molecular_populations(p)
     out["chain_pop"], out["chain_iters"], out["chain_conv"] = cp, cst["iters"].copy(), cst["converged"].copy()
     return out

@@ -21,7 +21,7 @@ def adapter():
     return C.CDLL(SO)
 
 
-@pytest.mark.parametrize("name", ["generic", "oh", "oh_overlap", "ch3oh_small", "h2o_small"])
+@pytest.mark.parametrize("name", ["generic", "oh", "oh_overlap", "ch3oh_small", "h2o_small", "nh3", "h2co"])
 def test_flatten_round_trip(adapter, problems, name):
     p = problems(name, 3)
     d, h1 = p.desc()
@@ -106,3 +106,26 @@ def test_gpu_scheme_virtuals_through_base_pointer(adapter, ref, problems, name):
     assert rel_err(new, new_o[lay], 1e-30) < 1e-9
     assert abs(eq.value - eq_o[lay]) <= 1e-9 * abs(eq_o[lay]) + 1e-13 * scale
     assert np.allclose(J, J_o, rtol=1e-10, atol=1e-300)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["ch3oh_small", "oh_overlap", "h2o_small"])
+def test_lim_luminosity_through_adapter(adapter, case):
+    """lim_luminosity_lvg_gpu fills the reference's transition_data_container; its own calc_saturation_depth follows."""
+    import golden_cases as G
+    p = G.problem(case)
+    gold = G.load(case)
+    d, h1 = p.desc()
+    s, h2 = p.layer_soa()
+    b = np.ascontiguousarray(gold["boundary"])
+    up = np.ascontiguousarray(gold["post_up"], dtype=np.int32); low = np.ascontiguousarray(gold["post_low"], dtype=np.int32)
+    T = len(up)
+    lum_arr = np.zeros((T, p.L)); loss = np.zeros((T, p.L)); pump = np.zeros((T, p.L)); lum = np.zeros(T); tau = np.zeros(T)
+    adapter.ref_adapter_lim_luminosity.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_double,
+                                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    rc = adapter.ref_adapter_lim_luminosity(C.addressof(d), C.addressof(s), b.ctypes.data, T, up.ctypes.data, low.ctypes.data, 1.0,
+                                            lum_arr.ctypes.data, loss.ctypes.data, pump.ctypes.data, lum.ctypes.data, tau.ctypes.data, 0)
+    assert rc == 0
+    for got, key in ((lum_arr, "lim_lum_arr"), (loss, "lim_loss_rate_arr"), (pump, "lim_pump_rate_arr"), (lum, "lim_lum"),
+                     (tau, "lim_tau_sat")):
+        assert np.allclose(got, gold[key], rtol=1e-9, atol=0.0, equal_nan=True), key

@@ -47,6 +47,9 @@ def gpu_results(solver_mod):
         post = m.maser_postpass(b, gold["post_up"], gold["post_low"])
         for k, v in post.items():
             got["post_" + k] = v
+        lim = m.lim_luminosity(b, gold["post_up"], gold["post_low"], beaming_factor=1.0, lay_nb_hg=post["scalars"][:, 4])
+        for k, v in lim.items():
+            got["lim_" + k] = v
         from radiative_transfer_b200 import abi
         cp, cst = m.calc_molecular_populations(start_mode=abi.RT_START_CHAINED)
         got["chain_pop"], got["chain_iters"], got["chain_conv"] = cp, cst["iters"].copy(), cst["converged"].copy()
@@ -102,9 +105,18 @@ def test_golden_maser_postpass(gpu_results, case):
         assert np.max(np.abs(got[k] - gold[k])) / scale < 1e-10, k
 
 
+@pytest.mark.parametrize("case", CASES)
+def test_golden_lim_luminosity(gpu_results, case):
+    """rt_lim_luminosity against lim_luminosity_lvg / calc_exc_temp / calc_saturation_depth of the reference."""
+    p, gold, got = gpu_results(case)
+    for k in ("lim_lum_arr", "lim_pump_eff_arr", "lim_loss_rate_arr", "lim_pump_rate_arr", "lim_emiss_coeff_arr",
+              "lim_exc_temp_arr", "lim_lum", "lim_tau_sat", "lim_temp_sat"):
+        assert np.allclose(got[k], gold[k], rtol=1e-9, atol=0.0, equal_nan=True), k
+
+
 # ---- live against the oracle, other sizes / seeds ---------------------------------------------------------------
 @pytest.mark.parametrize("name,L", [("generic", 9), ("oh", 5), ("oh_overlap", 5), ("ch3oh_small", 8), ("ch3oh_mid", 4),
-                                    ("h2o_small", 3)])
+                                    ("h2o_small", 3), ("nh3", 6), ("h2co", 6)])
 def test_live_solve_vs_oracle(solver_mod, best_checker, problems, name, L):
     p = problems(name, L)
     m = solver_mod.Model(p)

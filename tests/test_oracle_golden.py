@@ -87,3 +87,17 @@ def test_maser_postpass(computed, case):
     for k in ("post_inv", "post_gain", "post_scalars", "post_tau_vs_aspect", "post_tau_vs_freq"):
         scale = np.max(np.abs(gold[k])) + 1e-300
         assert np.max(np.abs(got[k] - gold[k])) / scale < 1e-10, k
+
+
+LIM_KEYS = ("lim_lum_arr", "lim_pump_eff_arr", "lim_loss_rate_arr", "lim_pump_rate_arr", "lim_emiss_coeff_arr", "lim_exc_temp_arr",
+            "lim_lum", "lim_tau_sat", "lim_temp_sat")
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_lim_luminosity(computed, case):
+    """lim_luminosity_lvg + calc_exc_temp + calc_saturation_depth."""
+    p, gold, got = computed(case)
+    assert np.array_equal(got["lim_lay_nb_hg"], gold["lim_lay_nb_hg"])
+    for k in LIM_KEYS:
+        assert np.allclose(got[k], gold[k], rtol=1e-9, atol=0.0, equal_nan=True), k
+
