@@ -16,11 +16,20 @@
 
 // shared-memory carve-up (doubles): M [Np][ldm] with ldm = Np + 1 (column Np = rhs; odd stride: conflict-free column
 // walks), pop [Np], yd [R], yu [R]
-__host__ __device__ inline size_t fused_smem_doubles(int Np, int R, bool with_c)
-{
-    return (size_t)Np * (Np + 1) + Np + 2 * (size_t)(R > 0 ? R : 1) + 64 + (with_c ? (size_t)Np * Np : 0);
-}
 __host__ __device__ inline bool fused_c_in_smem(int Np) { return Np <= 96; } // 2 x 73 KB at Np = 96
+// constants of the molecule staged once per CTA (read every iteration by the intensity and assembly phases): line records,
+// groups, and the per-row sparse lists; doubles first, then the int arrays
+__host__ __device__ inline size_t fused_const_doubles(const DevModel& d)
+{
+    const size_t R = d.R > 0 ? d.R : 1, G = d.G > 0 ? d.G : 1;
+    const size_t ints = 3 * G + 2 * R + (size_t)d.N + 1 + 4 * R;
+    return 3 * R + R * (d.ncomp > 0 ? d.ncomp : 1) + G + (ints + 1) / 2 + 2;
+}
+__host__ __device__ inline size_t fused_smem_doubles(const DevModel& d)
+{
+    const size_t Np = d.Np, R = d.R > 0 ? d.R : 1;
+    return Np * (Np + 1) + Np + 2 * R + 64 + (fused_c_in_smem(d.Np) ? Np * (Np + 1) : 0) + fused_const_doubles(d);
+}
 
 // Arg-max of the 64-bit keys of warp 0 (two REDUX), interchange of positions k <-> p in s_row, publication of the pivot's
 // physical row, the displaced row, p and 1/pivot for parity k & 1.  key = |a| bits with the low byte replaced by
@@ -61,6 +70,7 @@ __device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int Np
     }
 #pragma unroll
     for (int qi = NQ - 1; qi >= 0; qi--) {
+#pragma unroll 8
         for (int ii = 31; ii >= 0; ii--) {
             const int i = 32 * qi + ii;
             const double xi = __shfl_sync(0xffffffffu, b[qi] * rd[qi], ii);
@@ -74,7 +84,189 @@ __device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int Np
     for (int q = 0; q < NQ; q++) gnew[lane + 32 * q] = b[q];
 }
 
-__global__ void __launch_bounds__(FUSED_THREADS) k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
+// ------------------------------------------------------------------------------------------------------------------
+// Register-resident LU for Np = 32 * NQ <= 96 (OH N = 56, NH3, H2CO: Np = 64).  The matrix lives in the registers of the
+// CTA's 8 warps for the whole factorisation:
+//   warp w owns the columns c == w (mod 8)  (NS = Np / 8 column slots per thread, slot j <-> column w + 8 j),
+//   lane l owns the rows  l, l + 32, ...     (NQ rows per thread);  the right-hand side rides in b[NQ] (warp 0's is real).
+// Step k:  every warp gets the pivot row's values of ITS columns with one shuffle per slot (the pivot row is a lane, not
+// memory), the multipliers l_i = a[i][k] / pivot come from a 2 x Np double-buffered shared array written by the warp that
+// owns column k -- that warp ran one column AHEAD during step k-1 (updated column k first, REDUX arg-max on packed keys,
+// drcp, multipliers), so the CTA needs ONE barrier per column and no shared-memory traffic for the matrix itself.
+// Rows never move: pos[] is each row's position in the reference's row order (interchange k <-> p swaps two positions), it
+// gives the candidates (pos > k), the tie-break (smallest position) and, at the end, the row order of U.
+// Column slots are processed in blocks of 8 columns (one per warp); a finished block is stored to shared memory (U for the
+// back substitution) and the slots shift down, so the step body is the same code for every k of a block.
+// ------------------------------------------------------------------------------------------------------------------
+template <int NQ> __device__ __forceinline__ double sel_row(const double (&v)[NQ], int h)
+{
+    double r = v[0];
+#pragma unroll
+    for (int i = 1; i < NQ; i++) r = h == i ? v[i] : r;
+    return r;
+}
+template <int NQ> __device__ __forceinline__ int sel_rowi(const int (&v)[NQ], int h)
+{
+    int r = v[0];
+#pragma unroll
+    for (int i = 1; i < NQ; i++) r = h == i ? v[i] : r;
+    return r;
+}
+
+// executed by ONE warp: pivot of column k1 among the rows with pos >= k1; publishes the multipliers and {p, q, pos[p]}
+template <int NQ>
+__device__ __forceinline__ void reg_pivot(const double (&v)[NQ], const int (&pos)[NQ], int k1, int lane, double* sl, int* spv)
+{
+    unsigned long long mykey[NQ], key = 0ull;
+#pragma unroll
+    for (int i = 0; i < NQ; i++) {
+        mykey[i] = pos[i] >= k1 ? pivot_key(v[i], pos[i] - k1) : 0ull;
+        key = mykey[i] > key ? mykey[i] : key;
+    }
+    const unsigned hi = (unsigned)(key >> 32);
+    const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned lo = hi == mhi ? (unsigned)key : 0u;
+    const unsigned mlo = __reduce_max_sync(0xffffffffu, lo);
+    const unsigned long long win = ((unsigned long long)mhi << 32) | mlo;
+    int myi = -1, q1 = 0;
+#pragma unroll
+    for (int i = 0; i < NQ; i++) {
+        if (mykey[i] == win) myi = i;
+        const unsigned mq = __ballot_sync(0xffffffffu, pos[i] == k1);
+        if (mq) q1 = 32 * i + __ffs(mq) - 1;
+    }
+    const int wl = __ffs(__ballot_sync(0xffffffffu, myi >= 0)) - 1;
+    const int wi = __shfl_sync(0xffffffffu, myi, wl);
+    const int p1 = wl + 32 * wi;
+    const double piv = __shfl_sync(0xffffffffu, sel_row<NQ>(v, wi), wl);
+    const int pp1 = __shfl_sync(0xffffffffu, sel_rowi<NQ>(pos, wi), wl);
+    const double rp = piv != 0. ? __drcp_rn(piv) : 0.; // 0: zero pivot, the column is left as is
+#pragma unroll
+    for (int i = 0; i < NQ; i++) {
+        const int row = lane + 32 * i;
+        sl[row] = (pos[i] >= k1 && row != p1) ? v[i] * rp : 0.;
+    }
+    if (lane == 0) { spv[0] = p1; spv[1] = q1; spv[2] = pp1; }
+}
+
+// One LU step on the column slots [J0, NACT) of every warp
+template <int NQ, int NS, int J0, int NACT>
+__device__ __forceinline__ void reg_update(double (&a)[NQ][NS], const double (&l)[NQ], int ph, int pl)
+{
+#pragma unroll
+    for (int j = J0; j < NACT; j++) {
+        double col[NQ];
+#pragma unroll
+        for (int i = 0; i < NQ; i++) col[i] = a[i][j];
+        const double u = __shfl_sync(0xffffffffu, sel_row<NQ>(col, ph), pl);
+#pragma unroll
+        for (int i = 0; i < NQ; i++) a[i][j] -= l[i] * u;
+    }
+}
+
+template <int NQ, int NS, int KB>
+__device__ __forceinline__ void reg_lu_block(double (&a)[NQ][NS], double (&b)[NQ], int (&pos)[NQ], double* M, int ldm,
+                                             double (*s_l)[96], int (*s_pv)[4], int w, int lane)
+{
+    constexpr int Np = 32 * NQ, NACT = NS - KB;
+    for (int kk = 0; kk < 8; kk++) {
+        const int k = 8 * KB + kk, par = k & 1;
+        const int p = s_pv[par][0], q = s_pv[par][1], pp = s_pv[par][2];
+        double l[NQ];
+#pragma unroll
+        for (int i = 0; i < NQ; i++) {
+            const int row = lane + 32 * i;
+            l[i] = s_l[par][row];
+            pos[i] = row == p ? k : (row == q ? pp : pos[i]);
+        }
+        const int ph = p >> 5, pl = p & 31;
+        // slot 0 holds column w + 8 KB: already eliminated for w <= kk
+        {
+            double col[NQ];
+#pragma unroll
+            for (int i = 0; i < NQ; i++) col[i] = a[i][0];
+            const double u = __shfl_sync(0xffffffffu, sel_row<NQ>(col, ph), pl);
+            if (w > kk) {
+#pragma unroll
+                for (int i = 0; i < NQ; i++) a[i][0] -= l[i] * u;
+            }
+        }
+        if (NACT > 1) reg_update<NQ, NS, 1, (NACT > 1 ? 2 : 1)>(a, l, ph, pl);
+        // look-ahead: the owner of column k + 1 finds its pivot and publishes the multipliers for the next step
+        if (k + 1 < Np && w == ((kk + 1) & 7)) {
+            double v[NQ];
+#pragma unroll
+            for (int i = 0; i < NQ; i++) v[i] = (kk == 7 && NACT > 1) ? a[i][NACT > 1 ? 1 : 0] : a[i][0];
+            reg_pivot<NQ>(v, pos, k + 1, lane, s_l[par ^ 1], s_pv[par ^ 1]);
+        }
+        if (NACT > 2) reg_update<NQ, NS, 2, NACT>(a, l, ph, pl);
+        {
+            const double ub = __shfl_sync(0xffffffffu, sel_row<NQ>(b, ph), pl);
+#pragma unroll
+            for (int i = 0; i < NQ; i++) b[i] -= l[i] * ub;
+        }
+        __syncthreads();
+    }
+    // the finished column block goes to shared memory (U of the back substitution), the slots shift down
+#pragma unroll
+    for (int i = 0; i < NQ; i++) {
+        M[(size_t)(lane + 32 * i) * ldm + w + 8 * KB] = a[i][0];
+#pragma unroll
+        for (int j = 0; j + 1 < NACT; j++) a[i][j] = a[i][j + 1];
+    }
+}
+
+template <int NQ, int NS, int KB> struct RegLuBlocks {
+    static __device__ __forceinline__ void run(double (&a)[NQ][NS], double (&b)[NQ], int (&pos)[NQ], double* M, int ldm,
+                                               double (*s_l)[96], int (*s_pv)[4], int w, int lane)
+    {
+        reg_lu_block<NQ, NS, KB>(a, b, pos, M, ldm, s_l, s_pv, w, lane);
+        RegLuBlocks<NQ, NS, KB + 1>::run(a, b, pos, M, ldm, s_l, s_pv, w, lane);
+    }
+};
+template <int NQ, int NS> struct RegLuBlocks<NQ, NS, NS> {
+    static __device__ __forceinline__ void run(double (&)[NQ][NS], double (&)[NQ], int (&)[NQ], double*, int, double (*)[96], int (*)[4], int, int) {}
+};
+
+// M (shared, [Np][ldm], rhs in column Np) -> U in place (physical rows), eliminated rhs in column Np, s_row[pos] = row.
+// All FUSED_THREADS threads call it; ends with a barrier.
+template <int NQ>
+__device__ __forceinline__ void fused_lu_regs(double* M, int ldm, short* s_row, double (*s_l)[96], int (*s_pv)[4], int w, int lane)
+{
+    constexpr int Np = 32 * NQ, NS = Np / 8;
+    double a[NQ][NS], b[NQ];
+    int pos[NQ];
+#pragma unroll
+    for (int i = 0; i < NQ; i++) {
+        const double* Mr = M + (size_t)(lane + 32 * i) * ldm;
+#pragma unroll
+        for (int j = 0; j < NS; j++) a[i][j] = Mr[w + 8 * j];
+        b[i] = Mr[Np];
+        pos[i] = lane + 32 * i;
+    }
+    if (w == 0) {
+        double v[NQ];
+#pragma unroll
+        for (int i = 0; i < NQ; i++) v[i] = a[i][0];
+        reg_pivot<NQ>(v, pos, 0, lane, s_l[0], s_pv[0]);
+    }
+    __syncthreads();
+    RegLuBlocks<NQ, NS, 0>::run(a, b, pos, M, ldm, s_l, s_pv, w, lane);
+    if (w == 0) {
+#pragma unroll
+        for (int i = 0; i < NQ; i++) {
+            M[(size_t)(lane + 32 * i) * ldm + Np] = b[i];
+            s_row[pos[i]] = (short)(lane + 32 * i);
+        }
+    }
+    __syncthreads();
+}
+
+// LUV: 1..3 = register-resident LU with NQ = LUV (Np = 32 LUV), 0 = LU in shared memory (any Np <= 160).  One kernel per
+// variant so that the register allocation of the small, common sizes (two CTAs per SM) is not set by the large ones.
+template <int LUV>
+__global__ void __launch_bounds__(FUSED_THREADS, (LUV == 1 || LUV == 2) ? 2 : 1)
+k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
 {
     const int a = blockIdx.x;
     if (a >= nlay || a >= *d.n_active) return;
@@ -87,15 +279,37 @@ __global__ void __launch_bounds__(FUSED_THREADS) k_fused_solve(DevModel d, int n
     double* s_yu = s_yd + (R > 0 ? R : 1);
     __shared__ short s_row[160];  // position -> physical row of the LU
     __shared__ FusedPiv s_piv[2]; // pivot of the column, double-buffered by column parity
+    __shared__ double s_l[2][96]; // register-resident LU (Np <= 96): multipliers of the column, double-buffered
+    __shared__ int s_pv[2][4];    //   {pivot row, row at position k, position of the pivot row}
     __shared__ double s_eq[FUSED_THREADS / 32];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // the collisional matrix of the layer is constant over the iteration: staged in shared memory when it fits
     const double* C = d.Cmat + (size_t)lay * Np * Np;
+    int ldc = Np;
+    double* arena = s_yu + (R > 0 ? R : 1);
     if (fused_c_in_smem(Np)) {
-        double* s_C = s_yu + (R > 0 ? R : 1);
-        for (int e = tid; e < Np * Np; e += FUSED_THREADS) s_C[e] = C[e];
+        double* s_C = arena;
+        ldc = Np + 1; // odd stride: the assembly reads 8 rows per warp
+        for (int e = tid; e < Np * Np; e += FUSED_THREADS) s_C[(e / Np) * ldc + e % Np] = C[e];
         C = s_C;
+        arena += (size_t)Np * ldc;
     }
+    // molecule constants -> shared memory (fused_const_doubles)
+    const int Rn = R > 0 ? R : 1, Gn = d.G > 0 ? d.G : 1, nc = d.ncomp > 0 ? d.ncomp : 1, nnz = d.row_ptr[N];
+    double* c_Aul = arena; double* c_Alu = c_Aul + Rn; double* c_E = c_Alu + Rn; double* c_sig = c_E + Rn;
+    double* c_dxn = c_sig + (size_t)Rn * nc;
+    int* c_grp = (int*)(c_dxn + Gn); int* c_tru = c_grp + 3 * Gn; int* c_trl = c_tru + Rn; int* c_rptr = c_trl + Rn;
+    int* c_rcol = c_rptr + N + 1; int* c_rline = c_rcol + 2 * Rn;
+    for (int e = tid; e < R; e += FUSED_THREADS) {
+        c_Aul[e] = d.tr_Aul[e]; c_Alu[e] = d.tr_Alu[e]; c_E[e] = d.tr_E[e]; c_tru[e] = d.tr_u[e]; c_trl[e] = d.tr_l[e];
+        for (int k = 0; k < d.ncomp; k++) c_sig[(size_t)e * d.ncomp + k] = d.tr_sigma[(size_t)e * d.ncomp + k];
+    }
+    for (int e = tid; e < d.G; e += FUSED_THREADS) {
+        c_dxn[e] = d.grp_dxn[e];
+        c_grp[3 * e] = d.grp[3 * e]; c_grp[3 * e + 1] = d.grp[3 * e + 1]; c_grp[3 * e + 2] = d.grp[3 * e + 2];
+    }
+    for (int e = tid; e <= N; e += FUSED_THREADS) c_rptr[e] = d.row_ptr[e];
+    for (int e = tid; e < nnz; e += FUSED_THREADS) { c_rcol[e] = d.row_col[e]; c_rline[e] = d.row_line[e]; }
     double* gpop = d.pop + (size_t)lay * N;
     double* gnew = d.rhs + (size_t)lay * Np;
     const LayerCtx ctx = dev_layer_ctx(d, lay);
@@ -106,60 +320,67 @@ __global__ void __launch_bounds__(FUSED_THREADS) k_fused_solve(DevModel d, int n
         __syncthreads();
         // ---- K1a: mean intensities -> radiative rates (iteration_lvg.cpp:163-185, :428-501) ------------------------
         for (int gi = tid; gi < d.G; gi += FUSED_THREADS) {
-            const int nb = d.grp[3 * gi], la = d.grp[3 * gi + 1];
-            const int u1 = d.tr_u[la], l1 = d.tr_l[la];
-            const double A1ul = d.tr_Aul[la], A1lu = d.tr_Alu[la];
+            const int nb = c_grp[3 * gi], la = c_grp[3 * gi + 1];
+            const int u1 = c_tru[la], l1 = c_trl[la];
+            const double A1ul = c_Aul[la], A1lu = c_Alu[la];
             if (nb == 1) {
-                const double J = dev_intensity_single(d, ctx, d.tr_E[la], A1ul, A1lu, s_pop[u1], s_pop[l1], d.tr_sigma + (size_t)la * d.ncomp);
+                const double J = dev_intensity_single(d, ctx, c_E[la], A1ul, A1lu, s_pop[u1], s_pop[l1], c_sig + (size_t)la * d.ncomp);
                 s_yd[la] = A1ul * (1. + J);
                 s_yu[la] = A1lu * J;
             }
             else {
-                const int lb = d.grp[3 * gi + 2];
-                const int u2 = d.tr_u[lb], l2 = d.tr_l[lb];
-                const double A2ul = d.tr_Aul[lb], A2lu = d.tr_Alu[lb];
+                const int lb = c_grp[3 * gi + 2];
+                const int u2 = c_tru[lb], l2 = c_trl[lb];
+                const double A2ul = c_Aul[lb], A2lu = c_Alu[lb];
                 double J1, J2;
-                dev_intensity_pair(d, ctx, d.tr_E[la], d.grp_dxn[gi], A1ul, A1lu, A2ul, A2lu, s_pop[u1], s_pop[l1], s_pop[u2], s_pop[l2],
-                                   d.tr_sigma + (size_t)la * d.ncomp, J1, J2);
+                dev_intensity_pair(d, ctx, c_E[la], c_dxn[gi], A1ul, A1lu, A2ul, A2lu, s_pop[u1], s_pop[l1], s_pop[u2], s_pop[l2],
+                                   c_sig + (size_t)la * d.ncomp, J1, J2);
                 s_yd[la] = A1ul * (1. + J1); s_yu[la] = A1lu * J1;
                 s_yd[lb] = A2ul * (1. + J2); s_yu[lb] = A2lu * J2;
             }
         }
         __syncthreads();
         // ---- K1b: M = C + R, row 0 = 1, rhs = e0, df = e0 - M pop (iteration_lvg.cpp:112-161); one warp per row ------
+        // four lanes per row: 64 rows in flight, two shuffle steps per reduction
         double eqmax = 0.;
-        for (int row = warp; row < Np; row += FUSED_THREADS / 32) {
-            double* Mrow = M + (size_t)row * ldm;
-            const double* Crow = C + (size_t)row * Np;
-            double dot = 0.;
-            if (row == 0) {
-                for (int j = lane; j < Np; j += 32) { const double v = j < N ? 1. : 0.; Mrow[j] = v; dot += v * s_pop[j]; }
-            }
-            else {
-                for (int j = lane; j < Np; j += 32) { const double c = Crow[j]; Mrow[j] = c; dot += c * s_pop[j]; }
-                if (row < N) {
-                    __syncwarp();
-                    double diag = 0.;
-                    for (int e = d.row_ptr[row] + lane; e < d.row_ptr[row + 1]; e += 32) {
-                        const int col = d.row_col[e], ln = d.row_line[e], line = ln >> 1;
-                        const double off = (ln & 1) ? s_yd[line] : s_yu[line];
-                        const double dg = (ln & 1) ? s_yu[line] : s_yd[line];
-                        Mrow[col] = Crow[col] + off;
-                        dot += off * s_pop[col];
-                        diag += dg;
+        {
+            const int q = tid & 3;
+            const unsigned gmask = 0xFu << (lane & ~3);
+            for (int row = tid >> 2; row < Np; row += FUSED_THREADS / 4) {
+                double* Mrow = M + (size_t)row * ldm;
+                const double* Crow = C + (size_t)row * ldc;
+                double dot = 0.;
+                if (row == 0) {
+                    for (int j = q; j < Np; j += 4) { const double v = j < N ? 1. : 0.; Mrow[j] = v; dot += v * s_pop[j]; }
+                }
+                else {
+                    for (int j = q; j < Np; j += 4) { const double c = Crow[j]; Mrow[j] = c; dot += c * s_pop[j]; }
+                    if (row < N) {
+                        __syncwarp(gmask); // the row's copy is complete before its radiative entries are patched
+                        double diag = 0.;
+                        for (int e = c_rptr[row] + q; e < c_rptr[row + 1]; e += 4) {
+                            const int col = c_rcol[e], ln = c_rline[e], line = ln >> 1;
+                            const double off = (ln & 1) ? s_yd[line] : s_yu[line];
+                            const double dg = (ln & 1) ? s_yu[line] : s_yd[line];
+                            Mrow[col] = Crow[col] + off;
+                            dot += off * s_pop[col];
+                            diag += dg;
+                        }
+                        diag += __shfl_xor_sync(gmask, diag, 1);
+                        diag += __shfl_xor_sync(gmask, diag, 2);
+                        if (q == 0) { Mrow[row] = Crow[row] - diag; dot -= diag * s_pop[row]; }
                     }
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) diag += __shfl_xor_sync(0xffffffffu, diag, o);
-                    if (lane == 0) { Mrow[row] = Crow[row] - diag; dot -= diag * s_pop[row]; }
+                }
+                dot += __shfl_xor_sync(gmask, dot, 1);
+                dot += __shfl_xor_sync(gmask, dot, 2);
+                if (q == 0) {
+                    Mrow[Np] = row == 0 ? 1. : 0.;
+                    if (row < N) eqmax = fmax(eqmax, fabs((row == 0 ? 1. : 0.) - dot));
                 }
             }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-            if (lane == 0) {
-                Mrow[Np] = row == 0 ? 1. : 0.;
-                if (row < N) eqmax = fmax(eqmax, fabs((row == 0 ? 1. : 0.) - dot));
-            }
         }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) eqmax = fmax(eqmax, __shfl_xor_sync(0xffffffffu, eqmax, o));
         if (lane == 0) s_eq[warp] = eqmax;
         __syncthreads();
         if (tid == 0) {
@@ -174,7 +395,8 @@ __global__ void __launch_bounds__(FUSED_THREADS) k_fused_solve(DevModel d, int n
         //    (packed 64-bit keys, two REDUX max), interchanges the two positions and computes 1/pivot;
         //  * warps 1-7 apply step k to columns k+2 .. Np (rhs) as a 14 x 16 thread grid.
         // Values that agree in their top 56 bits count as ties (relative difference < 3e-14: immaterial for the pivot).
-        {
+        if constexpr (LUV > 0) fused_lu_regs<LUV>(M, ldm, s_row, s_l, s_pv, warp, lane); // Np = 64: OH, NH3, H2CO
+        else {
             for (int r = tid; r < Np; r += FUSED_THREADS) s_row[r] = (short)r;
             __syncthreads();
             if (warp == 0) {
@@ -220,13 +442,9 @@ __global__ void __launch_bounds__(FUSED_THREADS) k_fused_solve(DevModel d, int n
             }
         }
         if (warp == 0) {
-            switch (Np >> 5) {
-            case 1: fused_backsolve<1>(M, ldm, Np, s_row, gnew, lane); break;
-            case 2: fused_backsolve<2>(M, ldm, Np, s_row, gnew, lane); break;
-            case 3: fused_backsolve<3>(M, ldm, Np, s_row, gnew, lane); break;
-            case 4: fused_backsolve<4>(M, ldm, Np, s_row, gnew, lane); break;
-            default: fused_backsolve<5>(M, ldm, Np, s_row, gnew, lane); break;
-            }
+            if constexpr (LUV > 0) fused_backsolve<LUV>(M, ldm, Np, s_row, gnew, lane);
+            else if (Np == 128) fused_backsolve<4>(M, ldm, Np, s_row, gnew, lane);
+            else fused_backsolve<5>(M, ldm, Np, s_row, gnew, lane);
         }
         __syncthreads();
         // ---- K3: controller step (iteration_control.h:84-137), shared with the multi-kernel path --------------------
@@ -238,15 +456,25 @@ __global__ void __launch_bounds__(FUSED_THREADS) k_fused_solve(DevModel d, int n
 void launch_fused_solve(const DevModel& d, cudaStream_t s, int nlay, int accel, int max_iter, double min_err)
 {
     g_rt_launches++;
-    k_fused_solve<<<nlay, FUSED_THREADS, fused_smem_doubles(d.Np, d.R, fused_c_in_smem(d.Np)) * sizeof(double), s>>>(d, nlay, accel, max_iter, min_err);
+    const size_t smem = fused_smem_doubles(d) * sizeof(double);
+    switch (d.Np) {
+    case 32: k_fused_solve<1><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
+    case 64: k_fused_solve<2><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
+    case 96: k_fused_solve<3><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
+    default: k_fused_solve<0><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+    }
 }
 
 bool fused_supported(const DevModel& d)
 {
-    return d.Np <= 160 && fused_smem_doubles(d.Np, d.R, fused_c_in_smem(d.Np)) * sizeof(double) <= 220 * 1024;
+    return d.Np <= 160 && fused_smem_doubles(d) * sizeof(double) <= 220 * 1024;
 }
 
 cudaError_t fused_kernels_init()
 {
-    return cudaFuncSetAttribute(k_fused_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(k_fused_solve<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_solve<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_solve<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_solve<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    return e;
 }
