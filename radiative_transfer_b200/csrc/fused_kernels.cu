@@ -12,6 +12,7 @@
 #include "controller.cuh"
 #include "physics.cuh"
 
+#define FUSED_DYN_SMEM_MAX (210 * 1024) // + up to 13.3 KB static (publication ring) stays under the 227 KB per-CTA limit
 #define FUSED_THREADS CTL_THREADS // the controller device code is written for CTL_THREADS cooperating threads
 
 // shared-memory carve-up (doubles): M [Np][ldm] with ldm = Np + 1 (column Np = rhs; odd stride: conflict-free column
@@ -22,8 +23,12 @@ __host__ __device__ inline bool fused_c_in_smem(int Np) { return Np <= 96; } // 
 __host__ __device__ inline size_t fused_const_doubles(const DevModel& d)
 {
     const size_t R = d.R > 0 ? d.R : 1, G = d.G > 0 ? d.G : 1;
-    const size_t ints = 3 * G + 2 * R + (size_t)d.N + 1 + 4 * R;
-    return 3 * R + R * (d.ncomp > 0 ? d.ncomp : 1) + G + (ints + 1) / 2 + 2;
+    const size_t ints = 3 * G + 2 * R + (size_t)d.N + 1 + 4 * R + 2 * G /* tasks */;
+    size_t axes = (size_t)d.lvg.nb_d + d.lvg.nb_g;
+    if (d.scheme == RT_SCHEME_LINE_OVERLAP)
+        for (int t = 0; t < 2; t++) axes += (size_t)d.ov[t].nb_d + d.ov[t].nb_dx + d.ov[t].nb_gr + d.ov[t].nb_g;
+    const size_t halves = d.scheme == RT_SCHEME_LINE_OVERLAP ? 6 * G : 0;
+    return 3 * R + R * (d.ncomp > 0 ? d.ncomp : 1) + G + axes + halves + (ints + 1) / 2 + 2;
 }
 __host__ __device__ inline size_t fused_smem_doubles(const DevModel& d)
 {
@@ -298,8 +303,37 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     const int Rn = R > 0 ? R : 1, Gn = d.G > 0 ? d.G : 1, nc = d.ncomp > 0 ? d.ncomp : 1, nnz = d.row_ptr[N];
     double* c_Aul = arena; double* c_Alu = c_Aul + Rn; double* c_E = c_Alu + Rn; double* c_sig = c_E + Rn;
     double* c_dxn = c_sig + (size_t)Rn * nc;
-    int* c_grp = (int*)(c_dxn + Gn); int* c_tru = c_grp + 3 * Gn; int* c_trl = c_tru + Rn; int* c_rptr = c_trl + Rn;
-    int* c_rcol = c_rptr + N + 1; int* c_rline = c_rcol + 2 * Rn;
+    // axes of the escape-probability tables (binary searches every iteration), halves of the pair evaluations
+    DevLvg lvg = d.lvg;
+    DevOverlap ov0 = d.ov[0], ov1 = d.ov[1];
+    double* c_ax = c_dxn + Gn;
+    {
+        double* a = c_ax;
+        for (int e = tid; e < lvg.nb_d; e += FUSED_THREADS) a[e] = d.lvg.delta[e];
+        lvg.delta = a; a += lvg.nb_d;
+        for (int e = tid; e < lvg.nb_g; e += FUSED_THREADS) a[e] = d.lvg.gamma[e];
+        lvg.gamma = a; a += lvg.nb_g;
+        if (d.scheme == RT_SCHEME_LINE_OVERLAP) {
+#pragma unroll
+            for (int t = 0; t < 2; t++) {
+                DevOverlap& o = t ? ov1 : ov0;
+                const DevOverlap& g = d.ov[t];
+                for (int e = tid; e < o.nb_d; e += FUSED_THREADS) a[e] = g.log_delta[e];
+                o.log_delta = a; a += o.nb_d;
+                for (int e = tid; e < o.nb_dx; e += FUSED_THREADS) a[e] = g.dx[e];
+                o.dx = a; a += o.nb_dx;
+                for (int e = tid; e < o.nb_gr; e += FUSED_THREADS) a[e] = g.gratio[e];
+                o.gratio = a; a += o.nb_gr;
+                for (int e = tid; e < o.nb_g; e += FUSED_THREADS) a[e] = g.gamma[e];
+                o.gamma = a; a += o.nb_g;
+            }
+        }
+        c_ax = a;
+    }
+    double* c_half = c_ax; // [2G][3]
+    int* c_grp = (int*)(c_half + (d.scheme == RT_SCHEME_LINE_OVERLAP ? 6 * Gn : 0)); int* c_tru = c_grp + 3 * Gn; int* c_trl = c_tru + Rn; int* c_rptr = c_trl + Rn;
+    int* c_rcol = c_rptr + N + 1; int* c_rline = c_rcol + 2 * Rn; int* c_task = c_rline + 2 * Rn; // [2G] group * 2 + half
+    __shared__ int s_ntask;
     for (int e = tid; e < R; e += FUSED_THREADS) {
         c_Aul[e] = d.tr_Aul[e]; c_Alu[e] = d.tr_Alu[e]; c_E[e] = d.tr_E[e]; c_tru[e] = d.tr_u[e]; c_trl[e] = d.tr_l[e];
         for (int k = 0; k < d.ncomp; k++) c_sig[(size_t)e * d.ncomp + k] = d.tr_sigma[(size_t)e * d.ncomp + k];
@@ -308,6 +342,22 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         c_dxn[e] = d.grp_dxn[e];
         c_grp[3 * e] = d.grp[3 * e]; c_grp[3 * e + 1] = d.grp[3 * e + 1]; c_grp[3 * e + 2] = d.grp[3 * e + 2];
     }
+    if (d.scheme != RT_SCHEME_LINE_OVERLAP) { // one task per line
+        for (int g = tid; g < d.G; g += FUSED_THREADS) c_task[g] = 2 * g;
+        if (tid == 0) s_ntask = d.G;
+    }
+    else {
+        __syncthreads();
+        if (tid == 0) { // one task per single line, two per overlapping pair
+            int nt = 0;
+            for (int g = 0; g < d.G; g++) {
+                c_task[nt++] = 2 * g;
+                if (c_grp[3 * g] == 2) c_task[nt++] = 2 * g + 1;
+            }
+            s_ntask = nt;
+        }
+    }
+    const bool same_axes = d.ov_same_axes != 0;
     for (int e = tid; e <= N; e += FUSED_THREADS) c_rptr[e] = d.row_ptr[e];
     for (int e = tid; e < nnz; e += FUSED_THREADS) { c_rcol[e] = d.row_col[e]; c_rline[e] = d.row_line[e]; }
     double* gpop = d.pop + (size_t)lay * N;
@@ -319,22 +369,41 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         for (int j = tid; j < Np; j += FUSED_THREADS) s_pop[j] = j < N ? gpop[j] : 0.;
         __syncthreads();
         // ---- K1a: mean intensities -> radiative rates (iteration_lvg.cpp:163-185, :428-501) ------------------------
-        for (int gi = tid; gi < d.G; gi += FUSED_THREADS) {
+        const int ntask = s_ntask;
+        for (int t = tid; t < ntask; t += FUSED_THREADS) {
+            const int gi = c_task[t] >> 1, half = c_task[t] & 1;
             const int nb = c_grp[3 * gi], la = c_grp[3 * gi + 1];
             const int u1 = c_tru[la], l1 = c_trl[la];
             const double A1ul = c_Aul[la], A1lu = c_Alu[la];
             if (nb == 1) {
-                const double J = dev_intensity_single(d, ctx, c_E[la], A1ul, A1lu, s_pop[u1], s_pop[l1], c_sig + (size_t)la * d.ncomp);
+                const double J = dev_intensity_single(d, lvg, ctx, c_E[la], A1ul, A1lu, s_pop[u1], s_pop[l1], c_sig + (size_t)la * d.ncomp);
                 s_yd[la] = A1ul * (1. + J);
                 s_yu[la] = A1lu * J;
             }
             else {
                 const int lb = c_grp[3 * gi + 2];
                 const int u2 = c_tru[lb], l2 = c_trl[lb];
-                const double A2ul = c_Aul[lb], A2lu = c_Alu[lb];
+                const PairCommon pc = dev_pair_common(d, ctx, c_E[la], c_dxn[gi], A1ul, A1lu, c_Aul[lb], c_Alu[lb], s_pop[u1], s_pop[l1],
+                                                      s_pop[u2], s_pop[l2], c_sig + (size_t)la * d.ncomp);
+                double e[3];
+                dev_pair_half(d, lvg, ov0, ov1, same_axes, pc, half, e);
+                double* h = c_half + 3 * (size_t)(2 * gi + half);
+                h[0] = e[0]; h[1] = e[1]; h[2] = e[2];
+            }
+        }
+        if (d.scheme == RT_SCHEME_LINE_OVERLAP) {
+            __syncthreads();
+            for (int gi = tid; gi < d.G; gi += FUSED_THREADS) {
+                if (c_grp[3 * gi] != 2) continue;
+                const int la = c_grp[3 * gi + 1], lb = c_grp[3 * gi + 2];
+                const int u1 = c_tru[la], l1 = c_trl[la], u2 = c_tru[lb], l2 = c_trl[lb];
+                const double A1ul = c_Aul[la], A1lu = c_Alu[la], A2ul = c_Aul[lb], A2lu = c_Alu[lb];
+                const PairCommon pc = dev_pair_common(d, ctx, c_E[la], c_dxn[gi], A1ul, A1lu, A2ul, A2lu, s_pop[u1], s_pop[l1],
+                                                      s_pop[u2], s_pop[l2], c_sig + (size_t)la * d.ncomp);
+                const double* h = c_half + 6 * (size_t)gi;
+                const double a[3] = {h[0], h[1], h[2]}, b[3] = {h[3], h[4], h[5]};
                 double J1, J2;
-                dev_intensity_pair(d, ctx, c_E[la], c_dxn[gi], A1ul, A1lu, A2ul, A2lu, s_pop[u1], s_pop[l1], s_pop[u2], s_pop[l2],
-                                   c_sig + (size_t)la * d.ncomp, J1, J2);
+                dev_pair_combine(d, pc, a, b, J1, J2);
                 s_yd[la] = A1ul * (1. + J1); s_yu[la] = A1lu * J1;
                 s_yd[lb] = A2ul * (1. + J2); s_yu[lb] = A2lu * J2;
             }
@@ -467,14 +536,19 @@ void launch_fused_solve(const DevModel& d, cudaStream_t s, int nlay, int accel, 
 
 bool fused_supported(const DevModel& d)
 {
-    return d.Np <= 160 && fused_smem_doubles(d) * sizeof(double) <= 220 * 1024;
+    return d.Np <= 160 && fused_smem_doubles(d) * sizeof(double) <= FUSED_DYN_SMEM_MAX;
+}
+
+template <int LUV> static cudaError_t fused_set_smem()
+{
+    return cudaFuncSetAttribute(k_fused_solve<LUV>, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_DYN_SMEM_MAX);
 }
 
 cudaError_t fused_kernels_init()
 {
-    cudaError_t e = cudaFuncSetAttribute(k_fused_solve<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_solve<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_solve<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fused_solve<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaError_t e = fused_set_smem<0>();
+    if (e == cudaSuccess) e = fused_set_smem<1>();
+    if (e == cudaSuccess) e = fused_set_smem<2>();
+    if (e == cudaSuccess) e = fused_set_smem<3>();
     return e;
 }

@@ -319,6 +319,11 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
             d.ov[q].gamma = dev_upload(m, o.gamma, o.nb_g, false);
             d.ov[q].p = dev_upload(m, o.p, (size_t)o.nb_d * o.nb_dx * o.nb_gr * o.nb_g, false);
         }
+        const rt_overlap_table &o1 = *src[0], &o2 = *src[1];
+        d.ov_same_axes = o1.nb_d == o2.nb_d && o1.nb_dx == o2.nb_dx && o1.nb_gr == o2.nb_gr && o1.nb_g == o2.nb_g
+                         && o1.delta_is_log10 == o2.delta_is_log10 && !memcmp(o1.delta, o2.delta, sizeof(double) * o1.nb_d)
+                         && !memcmp(o1.dx, o2.dx, sizeof(double) * o1.nb_dx) && !memcmp(o1.gratio, o2.gratio, sizeof(double) * o1.nb_gr)
+                         && !memcmp(o1.gamma, o2.gamma, sizeof(double) * o1.nb_g);
     }
     if (cudaDeviceSynchronize() != cudaSuccess || !m->last_error.empty()) {
         g_create_error = m->last_error.empty() ? "CUDA failure in rt_model_create" : m->last_error;

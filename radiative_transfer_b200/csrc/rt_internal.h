@@ -55,6 +55,7 @@ struct DevModel {
     DevTable tab[RT_MAX_TABLES];
     DevLvg lvg;
     DevOverlap ov[2];
+    int ov_same_axes;        // both overlap tables on bitwise identical grids: one index search serves both
     // layers (SoA, [L])
     const double *temp_n, *temp_el, *mol_conc, *vel_width, *vel_grad, *dust_conc /*[L][ncomp]*/;
     const double* conc;      // [L][K] partner concentrations (set_gas_param)
