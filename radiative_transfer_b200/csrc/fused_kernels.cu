@@ -110,48 +110,60 @@ template <int NQ> __device__ __forceinline__ double sel_row(const double (&v)[NQ
     for (int i = 1; i < NQ; i++) r = h == i ? v[i] : r;
     return r;
 }
-template <int NQ> __device__ __forceinline__ int sel_rowi(const int (&v)[NQ], int h)
-{
-    int r = v[0];
-#pragma unroll
-    for (int i = 1; i < NQ; i++) r = h == i ? v[i] : r;
-    return r;
-}
-
-// executed by ONE warp: pivot of column k1 among the rows with pos >= k1; publishes the multipliers and {p, q, pos[p]}
+// executed by ONE warp: pivot of column k1 among the rows not yet used as pivots (`done` bit i = row lane + 32 i is used);
+// publishes the multipliers of the column and the pivot row.
+// Fast path: one REDUX over the top 32 bits of |a| (sign stripped); when exactly one row holds that maximum it is the
+// pivot.  Otherwise (two rows agree in 20 mantissa bits, or the column is zero) packed 64-bit keys decide: larger |a| in the
+// top 56 bits, exact ties -> smallest row index (the scalar loop takes the smallest position: same magnitude, the choice
+// only reorders rounding).
 template <int NQ>
-__device__ __forceinline__ void reg_pivot(const double (&v)[NQ], const int (&pos)[NQ], int k1, int lane, double* sl, int* spv)
+__device__ __forceinline__ void reg_pivot(const double (&v)[NQ], unsigned done, int k1, int lane, double* sl, int* spv, short* s_row)
 {
-    unsigned long long mykey[NQ], key = 0ull;
+    unsigned hmax = 0u;
+    int bi = 0;
+    bool dup = false;
 #pragma unroll
     for (int i = 0; i < NQ; i++) {
-        mykey[i] = pos[i] >= k1 ? pivot_key(v[i], pos[i] - k1) : 0ull;
-        key = mykey[i] > key ? mykey[i] : key;
+        const unsigned h = (done >> i) & 1u ? 0u : ((unsigned)__double2hiint(v[i]) & 0x7fffffffu);
+        dup = (h == hmax && h != 0u) || (dup && h < hmax);
+        if (h > hmax) { hmax = h; bi = i; }
     }
-    const unsigned hi = (unsigned)(key >> 32);
-    const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
-    const unsigned lo = hi == mhi ? (unsigned)key : 0u;
-    const unsigned mlo = __reduce_max_sync(0xffffffffu, lo);
-    const unsigned long long win = ((unsigned long long)mhi << 32) | mlo;
-    int myi = -1, q1 = 0;
+    const unsigned mhi = __reduce_max_sync(0xffffffffu, hmax);
+    const unsigned vote = __ballot_sync(0xffffffffu, hmax == mhi);
+    const unsigned vdup = __ballot_sync(0xffffffffu, dup && hmax == mhi);
+    int wl, wi;
+    if (mhi != 0u && __popc(vote) == 1 && vdup == 0u) {
+        wl = __ffs(vote) - 1;
+        wi = __shfl_sync(0xffffffffu, bi, wl);
+    }
+    else {
+        unsigned long long mykey[NQ], key = 0ull;
 #pragma unroll
-    for (int i = 0; i < NQ; i++) {
-        if (mykey[i] == win) myi = i;
-        const unsigned mq = __ballot_sync(0xffffffffu, pos[i] == k1);
-        if (mq) q1 = 32 * i + __ffs(mq) - 1;
+        for (int i = 0; i < NQ; i++) {
+            mykey[i] = (done >> i) & 1u ? 0ull : pivot_key(v[i], lane + 32 * i);
+            key = mykey[i] > key ? mykey[i] : key;
+        }
+        const unsigned hi = (unsigned)(key >> 32);
+        const unsigned khi = __reduce_max_sync(0xffffffffu, hi);
+        const unsigned lo = hi == khi ? (unsigned)key : 0u;
+        const unsigned klo = __reduce_max_sync(0xffffffffu, lo);
+        const unsigned long long win = ((unsigned long long)khi << 32) | klo;
+        int myi = -1;
+#pragma unroll
+        for (int i = 0; i < NQ; i++)
+            if (mykey[i] == win) myi = i;
+        wl = __ffs(__ballot_sync(0xffffffffu, myi >= 0)) - 1;
+        wi = __shfl_sync(0xffffffffu, myi, wl);
     }
-    const int wl = __ffs(__ballot_sync(0xffffffffu, myi >= 0)) - 1;
-    const int wi = __shfl_sync(0xffffffffu, myi, wl);
     const int p1 = wl + 32 * wi;
     const double piv = __shfl_sync(0xffffffffu, sel_row<NQ>(v, wi), wl);
-    const int pp1 = __shfl_sync(0xffffffffu, sel_rowi<NQ>(pos, wi), wl);
     const double rp = piv != 0. ? __drcp_rn(piv) : 0.; // 0: zero pivot, the column is left as is
 #pragma unroll
     for (int i = 0; i < NQ; i++) {
         const int row = lane + 32 * i;
-        sl[row] = (pos[i] >= k1 && row != p1) ? v[i] * rp : 0.;
+        sl[row] = ((done >> i) & 1u) || row == p1 ? 0. : v[i] * rp;
     }
-    if (lane == 0) { spv[0] = p1; spv[1] = q1; spv[2] = pp1; }
+    if (lane == 0) { spv[0] = p1; s_row[k1] = (short)p1; }
 }
 
 // One LU step on the column slots [J0, NACT) of every warp
@@ -169,20 +181,24 @@ __device__ __forceinline__ void reg_update(double (&a)[NQ][NS], const double (&l
     }
 }
 
+// Steps 8 KB .. 8 KB + 7, one CTA barrier per step; the publications (multipliers + pivot row) are double-buffered by
+// column parity.  Measured alternatives, all slower or equal on B200 (OH N = 56, per iteration): warps decoupled through
+// per-step mbarriers so that the rank-1 updates trail behind the pivot chain: 30 us vs 31 us; spinning on a shared-memory
+// counter instead of mbarriers: 155 us; speculative reciprocals of every lane's candidate: slower.  The step is bound by the
+// instruction count of the warp that searches the pivot (~3 cycles per dependent instruction), not by the barrier.
 template <int NQ, int NS, int KB>
-__device__ __forceinline__ void reg_lu_block(double (&a)[NQ][NS], double (&b)[NQ], int (&pos)[NQ], double* M, int ldm,
-                                             double (*s_l)[96], int (*s_pv)[4], int w, int lane)
+__device__ __forceinline__ void reg_lu_block(double (&a)[NQ][NS], double (&b)[NQ], unsigned& done, double* M, int ldm, short* s_row,
+                                             double* s_l, int (*s_pv)[4], int w, int lane)
 {
     constexpr int Np = 32 * NQ, NACT = NS - KB;
     for (int kk = 0; kk < 8; kk++) {
         const int k = 8 * KB + kk, par = k & 1;
-        const int p = s_pv[par][0], q = s_pv[par][1], pp = s_pv[par][2];
+        const int p = s_pv[par][0];
         double l[NQ];
 #pragma unroll
         for (int i = 0; i < NQ; i++) {
-            const int row = lane + 32 * i;
-            l[i] = s_l[par][row];
-            pos[i] = row == p ? k : (row == q ? pp : pos[i]);
+            l[i] = s_l[par * Np + lane + 32 * i];
+            done |= (unsigned)(lane + 32 * i == p) << i;
         }
         const int ph = p >> 5, pl = p & 31;
         // slot 0 holds column w + 8 KB: already eliminated for w <= kk
@@ -202,7 +218,7 @@ __device__ __forceinline__ void reg_lu_block(double (&a)[NQ][NS], double (&b)[NQ
             double v[NQ];
 #pragma unroll
             for (int i = 0; i < NQ; i++) v[i] = (kk == 7 && NACT > 1) ? a[i][NACT > 1 ? 1 : 0] : a[i][0];
-            reg_pivot<NQ>(v, pos, k + 1, lane, s_l[par ^ 1], s_pv[par ^ 1]);
+            reg_pivot<NQ>(v, done, k + 1, lane, s_l + (par ^ 1) * Np, s_pv[par ^ 1], s_row);
         }
         if (NACT > 2) reg_update<NQ, NS, 2, NACT>(a, l, ph, pl);
         {
@@ -222,47 +238,43 @@ __device__ __forceinline__ void reg_lu_block(double (&a)[NQ][NS], double (&b)[NQ
 }
 
 template <int NQ, int NS, int KB> struct RegLuBlocks {
-    static __device__ __forceinline__ void run(double (&a)[NQ][NS], double (&b)[NQ], int (&pos)[NQ], double* M, int ldm,
-                                               double (*s_l)[96], int (*s_pv)[4], int w, int lane)
+    static __device__ __forceinline__ void run(double (&a)[NQ][NS], double (&b)[NQ], unsigned& done, double* M, int ldm, short* s_row,
+                                               double* s_l, int (*s_pv)[4], int w, int lane)
     {
-        reg_lu_block<NQ, NS, KB>(a, b, pos, M, ldm, s_l, s_pv, w, lane);
-        RegLuBlocks<NQ, NS, KB + 1>::run(a, b, pos, M, ldm, s_l, s_pv, w, lane);
+        reg_lu_block<NQ, NS, KB>(a, b, done, M, ldm, s_row, s_l, s_pv, w, lane);
+        RegLuBlocks<NQ, NS, KB + 1>::run(a, b, done, M, ldm, s_row, s_l, s_pv, w, lane);
     }
 };
 template <int NQ, int NS> struct RegLuBlocks<NQ, NS, NS> {
-    static __device__ __forceinline__ void run(double (&)[NQ][NS], double (&)[NQ], int (&)[NQ], double*, int, double (*)[96], int (*)[4], int, int) {}
+    static __device__ __forceinline__ void run(double (&)[NQ][NS], double (&)[NQ], unsigned&, double*, int, short*, double*, int (*)[4], int, int) {}
 };
 
-// M (shared, [Np][ldm], rhs in column Np) -> U in place (physical rows), eliminated rhs in column Np, s_row[pos] = row.
-// All FUSED_THREADS threads call it; ends with a barrier.
+// M (shared, [Np][ldm], rhs in column Np) -> U in place (physical rows), eliminated rhs in column Np, s_row[k] = pivot row
+// of step k.  All FUSED_THREADS threads call it; ends with a barrier.
 template <int NQ>
-__device__ __forceinline__ void fused_lu_regs(double* M, int ldm, short* s_row, double (*s_l)[96], int (*s_pv)[4], int w, int lane)
+__device__ __forceinline__ void fused_lu_regs(double* M, int ldm, short* s_row, double* s_l, int (*s_pv)[4], int w, int lane)
 {
     constexpr int Np = 32 * NQ, NS = Np / 8;
     double a[NQ][NS], b[NQ];
-    int pos[NQ];
+    unsigned done = 0u;
 #pragma unroll
     for (int i = 0; i < NQ; i++) {
         const double* Mr = M + (size_t)(lane + 32 * i) * ldm;
 #pragma unroll
         for (int j = 0; j < NS; j++) a[i][j] = Mr[w + 8 * j];
         b[i] = Mr[Np];
-        pos[i] = lane + 32 * i;
     }
     if (w == 0) {
         double v[NQ];
 #pragma unroll
         for (int i = 0; i < NQ; i++) v[i] = a[i][0];
-        reg_pivot<NQ>(v, pos, 0, lane, s_l[0], s_pv[0]);
+        reg_pivot<NQ>(v, 0u, 0, lane, s_l, s_pv[0], s_row);
     }
     __syncthreads();
-    RegLuBlocks<NQ, NS, 0>::run(a, b, pos, M, ldm, s_l, s_pv, w, lane);
+    RegLuBlocks<NQ, NS, 0>::run(a, b, done, M, ldm, s_row, s_l, s_pv, w, lane);
     if (w == 0) {
 #pragma unroll
-        for (int i = 0; i < NQ; i++) {
-            M[(size_t)(lane + 32 * i) * ldm + Np] = b[i];
-            s_row[pos[i]] = (short)(lane + 32 * i);
-        }
+        for (int i = 0; i < NQ; i++) M[(size_t)(lane + 32 * i) * ldm + Np] = b[i];
     }
     __syncthreads();
 }
@@ -284,8 +296,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     double* s_yu = s_yd + (R > 0 ? R : 1);
     __shared__ short s_row[160];  // position -> physical row of the LU
     __shared__ FusedPiv s_piv[2]; // pivot of the column, double-buffered by column parity
-    __shared__ double s_l[2][96]; // register-resident LU (Np <= 96): multipliers of the column, double-buffered
-    __shared__ int s_pv[2][4];    //   {pivot row, row at position k, position of the pivot row}
+    __shared__ double s_l[2 * (LUV > 0 ? 32 * LUV : 1)]; // register-resident LU: multipliers of the column, double-buffered
+    __shared__ int s_pv[2][4];                           //   pivot row of the column
     __shared__ double s_eq[FUSED_THREADS / 32];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // the collisional matrix of the layer is constant over the iteration: staged in shared memory when it fits
