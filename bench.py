@@ -27,8 +27,15 @@ import sys
 import threading
 import time
 
-# stdout carries exactly one JSON line: NCCL's banner ("NCCL version ...") and debug output go to stderr
+# stdout carries exactly one JSON line.  Libraries print there too (NCCL's "NCCL version ..." banner ignores
+# NCCL_DEBUG_FILE), so file descriptor 1 is pointed at stderr for the whole run and the JSON line goes to the saved one.
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line: str) -> None:
+    os.write(_REAL_STDOUT, (line + "\n").encode())
 
 import numpy as np
 
@@ -188,7 +195,7 @@ def run_reference(args):
                                    f"{cores} threads (layers are independent); models/s = layers/s / {p.L}"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(out), flush=True)
+    emit(json.dumps(out))
     return 0
 
 
@@ -369,7 +376,7 @@ def run_gpu(args):
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                                "sample": f"{info['layers']} evenly spaced layers of the slab solved to convergence on {cores} threads in "
                                          f"{sec:.1f} s (mean {info['iters_mean']:.0f} iterations); models/s = layers/s / {p_full.L}"}
-    print(json.dumps(out), flush=True)
+    emit(json.dumps(out))
     m.close()
     if dist is not None:
         dist.barrier()
