@@ -227,6 +227,12 @@ def run_gpu(args):
         from radiative_transfer_b200 import sharding
         lo, hi = sharding.layer_range(p_full.L, world, rank)
         p = p_full.sliced(lo, hi)
+    if args.batch > 1:
+        # sweep throughput mode: --batch M models per solve as ONE cloud of M*L independent layers (sharding.stack_clouds);
+        # the headline `value` is quoted at the default M = 1, the slab of BASELINE configs[1]
+        from radiative_transfer_b200 import sharding
+        p, _ = sharding.stack_clouds([p_full] * args.batch)
+        name += f" x {args.batch} models per solve"
     N, L = p.N, p.L
     m = solver.Model(p, device=local, upload_cloud=False)
     lay_pinned, keep = pinned_layers(p)
@@ -276,7 +282,7 @@ def run_gpu(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total_max = float(t.item())
     ms_per_step = ms_total_max / args.steps
-    models_per_step = n_gpus if args.mode == "sweep" else 1
+    models_per_step = n_gpus * args.batch if args.mode == "sweep" else 1
     value = models_per_step / (ms_per_step * 1e-3)
 
     # ---- e2e leg: host buffers through the C ABI ---------------------------------------------------------------------
@@ -329,7 +335,7 @@ def run_gpu(args):
                    "share": v["ms"] / ms_profiled}
     traffic = {}
     tf = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tf) and args.config == "ch3oh" and args.layers in (None, 0, 200):  # captured on this workload only
+    if os.path.exists(tf) and args.config == "ch3oh" and args.layers in (None, 0, 200) and args.batch == 1:  # captured on this workload only
         traffic = json.load(open(tf))
     top = max(kern, key=lambda k: kern[k]["ms_per_step"])
 
@@ -354,7 +360,7 @@ def run_gpu(args):
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if args.mode == "sweep" else "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": name, "start": "boundary", "accel": bool(p.accel), "max_iter": p.max_iter, "min_err": 1e-5,
-                   "mode": args.mode, "l2": "per-step working set (C and M matrices, 2 x %.0f MB) exceeds the 126 MB L2"
+                   "mode": args.mode, "models_per_solve": args.batch, "l2": "per-step working set (C and M matrices, 2 x %.0f MB) exceeds the 126 MB L2"
                    % (L * ((N + 31) // 32 * 32) ** 2 * 8 / 1e6),
                    "timing": "CUDA events on the library's stream around K steps; max over ranks; per-kernel times from a second pass "
                              "of the same K steps with an event pair around every kernel class"},
@@ -388,6 +394,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=1, help="models per solve (sweep mode): M slabs stacked into one cloud")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="ch3oh", choices=["ch3oh", "h2o", "oh", "oh_overlap"])

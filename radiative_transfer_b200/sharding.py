@@ -74,3 +74,57 @@ def sweep_assign(n_points: int, world: int, rank: int) -> List[int]:
     round-robin, the static analogue of the reference's `omp for schedule(dynamic,1)` over shock models
     (radiative_transfer.cpp:152-159).  No collective: every model is independent."""
     return list(range(rank, n_points, world))
+
+
+class SweepQueue:
+    """Dynamic hand-out of grid points to ranks: the direct analogue of the reference's
+    `#pragma omp parallel for schedule(dynamic,1)` over shock models (radiative_transfer.cpp:152-159).  Iteration counts
+    differ from model to model, so a static split leaves ranks idle at the end of a sweep; here every rank draws the next
+    unclaimed index from a shared counter.  The counter lives in the process group's key-value store (the rendezvous
+    TCPStore of torch.distributed: `add` is atomic), so no collective and no GPU traffic is involved.
+
+        for i in SweepQueue(n_points):        # on every rank
+            solve(grid_point(i))
+    """
+
+    def __init__(self, n_points: int, name: str = "rt_sweep", store=None):
+        import torch.distributed as dist
+        self.n = int(n_points)
+        self.key = f"{name}/next"
+        self._local = 0
+        self.store = store
+        if store is None and dist.is_available() and dist.is_initialized():
+            self.store = dist.distributed_c10d._get_default_store()
+
+    def __iter__(self):
+        return self
+
+    def __next__(self) -> int:
+        if self.store is None:  # single process
+            i, self._local = self._local, self._local + 1
+        else:
+            i = int(self.store.add(self.key, 1)) - 1
+        if i >= self.n:
+            raise StopIteration
+        return i
+
+
+def stack_clouds(problems):
+    """Several models of the SAME molecule as one cloud: layers are independent, so the layers of
+    M slabs concatenated are one batch of M*L layers for the solver -- the way to fill a GPU whose 148 SMs a single
+    200-layer slab leaves partly idle.  Returns (stacked problem, [(lo, hi) layer range of each model])."""
+    import copy
+    base = copy.copy(problems[0])
+    keys = list(base.layers.keys())
+    lay, ranges, lo = {}, [], 0
+    for k in keys:
+        v0 = base.layers[k]
+        if np.ndim(v0) == 0:
+            lay[k] = v0
+        else:
+            lay[k] = np.concatenate([np.asarray(q.layers[k]) for q in problems], axis=0)
+    for q in problems:
+        ranges.append((lo, lo + q.L))
+        lo += q.L
+    base.layers = lay
+    return base, ranges

@@ -70,3 +70,49 @@ def test_layer_range_and_sweep_assign():
             assert max(sizes) - min(sizes) <= 1
     pts = sorted(sum((sharding.sweep_assign(512, 8, k) for k in range(8)), []))
     assert pts == list(range(512))
+
+
+def _queue_worker(rank, world, port, n, q):
+    import sys, time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from radiative_transfer_b200 import sharding
+    mine = []
+    for i in sharding.SweepQueue(n):
+        mine.append(i)
+        time.sleep(0.002 * (1 + 3 * rank))  # rank 1 is the slow one: it must end up with fewer points
+    q.put((rank, mine))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sweep_queue_hands_every_point_out_once():
+    """Dynamic model-per-rank scheduling (the analogue of `omp for schedule(dynamic,1)`, radiative_transfer.cpp:152-159)."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    world, tcp, n = 2, _free_port(), 40
+    procs = [ctx.Process(target=_queue_worker, args=(r, world, tcp, n, q)) for r in range(world)]
+    for pr in procs:
+        pr.start()
+    got = dict(q.get(timeout=120) for _ in range(world))
+    for pr in procs:
+        pr.join(timeout=60)
+        assert pr.exitcode == 0
+    assert sorted(got[0] + got[1]) == list(range(n))
+    assert len(got[0]) > len(got[1]) > 0
+
+
+def test_sweep_queue_single_process_and_stack_clouds():
+    from radiative_transfer_b200 import sharding, synthetic
+    assert list(sharding.SweepQueue(5)) == [0, 1, 2, 3, 4]
+    a = synthetic.small("ch3oh_small", L=3)
+    b = synthetic.config_ch3oh(L=2, n_vt=2, n_k=6, n_j=8, cloud_kw=dict(t_hi=200.0))
+    s, ranges = sharding.stack_clouds([a, b])
+    assert s.L == 5 and ranges == [(0, 3), (3, 5)]
+    assert np.array_equal(s.layers["temp_n"][:3], a.layers["temp_n"]) and np.array_equal(s.layers["temp_n"][3:], b.layers["temp_n"])
+    assert s.layers["dust_conc"].shape == (5, a.layers["dust_conc"].shape[1])
