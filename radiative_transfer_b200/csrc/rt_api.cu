@@ -57,6 +57,21 @@ template <class T> static T* dev_upload(rt_model* m, const T* h, size_t n, bool 
     return p;
 }
 
+// scratch device buffers of one entry-point call: freed on every exit path (the CK macro returns early)
+struct DevScratch {
+    std::vector<void*> bufs;
+    ~DevScratch() { for (void* p : bufs) cudaFree(p); }
+    void* get(size_t bytes, const void* host = nullptr)
+    {
+        void* p = nullptr;
+        if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+        bufs.push_back(p);
+        if (host && cudaMemcpy(p, host, bytes, cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
+        return p;
+    }
+};
+#define NEED_BUF(ptr) do { if (!(ptr)) { m->last_error = "device scratch allocation / upload failed"; return RT_ERR_NOMEM; } } while (0)
+
 extern "C" {
 
 void rt_params_default(rt_params* p)
@@ -764,8 +779,9 @@ rt_status rt_assemble(rt_model* m, const double* pop, double* matrix, double* df
     const int L = d.L, N = d.N, Np = d.Np;
     rt_status r = rt_set_populations(m, pop);
     if (r) return r;
-    double* df_dev = nullptr;
-    CK(cudaMalloc(&df_dev, sizeof(double) * (size_t)L * N));
+    DevScratch scratch;
+    double* df_dev = (double*)scratch.get(sizeof(double) * (size_t)L * N);
+    NEED_BUF(df_dev);
     launch_set_active_range(d, m->stream, 0, L);
     launch_compact(d, m->stream);
     CK(cudaMemsetAsync(d.eq_bits, 0, sizeof(unsigned long long) * L, m->stream));
@@ -773,7 +789,6 @@ rt_status rt_assemble(rt_model* m, const double* pop, double* matrix, double* df
     launch_assemble(d, m->stream, L, df_dev);
     CK(cudaStreamSynchronize(m->stream));
     if (df) CK(cudaMemcpy(df, df_dev, sizeof(double) * (size_t)L * N, cudaMemcpyDeviceToHost));
-    cudaFree(df_dev);
     if (matrix) // strip the padding, layer by layer
         for (int l = 0; l < L; l++)
             CK(cudaMemcpy2D(matrix + (size_t)l * N * N, sizeof(double) * N, d.Mmat + (size_t)l * Np * d.ld, sizeof(double) * d.ld,
@@ -913,18 +928,15 @@ extern "C" rt_status rt_intensity(rt_model* m, int lay, int up, int low, const d
     std::vector<double> buf(1 + RT_MAX_DUST, 0.);
     const std::vector<double> sg = line_sigma(m, e1);
     for (int c = 0; c < d.ncomp; c++) buf[1 + c] = sg[c];
-    double *pop_dev = nullptr, *out_dev = nullptr;
-    CK(cudaMalloc(&pop_dev, sizeof(double) * N));
-    CK(cudaMalloc(&out_dev, sizeof(double) * buf.size()));
-    CK(cudaMemcpy(pop_dev, pop, sizeof(double) * N, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(out_dev, buf.data(), sizeof(double) * buf.size(), cudaMemcpyHostToDevice));
+    DevScratch scratch;
+    double* pop_dev = (double*)scratch.get(sizeof(double) * N, pop);
+    double* out_dev = (double*)scratch.get(sizeof(double) * buf.size(), buf.data());
+    NEED_BUF(pop_dev && out_dev);
     const std::vector<double>& A = m->h_einst;
     launch_intensity_single(d, m->stream, lay, u1, l1, A[(size_t)u1 * N + l1], A[(size_t)l1 * N + u1], u2, l2,
                             A[(size_t)u2 * N + l2], A[(size_t)l2 * N + u2], which, pop_dev, out_dev);
     CK(cudaStreamSynchronize(m->stream));
     CK(cudaMemcpy(intensity, out_dev, sizeof(double), cudaMemcpyDeviceToHost));
-    cudaFree(pop_dev);
-    cudaFree(out_dev);
     return RT_OK;
 }
 
@@ -951,9 +963,10 @@ extern "C" rt_status rt_maser_postpass(rt_model* m, const double* pop, int nb_tr
     const double dv = (vmax - vmin) / (nb_freq - 1.);
     double vel = vmin;
     for (int n = 0; n < nb_freq; n++, vel += dv) vgrid[n] = vel;
-    std::vector<void*> tmp;
-    auto up_d = [&](const void* h, size_t bytes) { void* p = nullptr; cudaMalloc(&p, bytes); cudaMemcpy(p, h, bytes, cudaMemcpyHostToDevice); tmp.push_back(p); return p; };
-    auto out_d = [&](size_t bytes) { void* p = nullptr; cudaMalloc(&p, bytes); tmp.push_back(p); return p; };
+    DevScratch scratch;
+    bool ok = true;
+    auto up_d = [&](const void* h, size_t bytes) { void* p = scratch.get(bytes, h); ok = ok && p; return p; };
+    auto out_d = [&](size_t bytes) { void* p = scratch.get(bytes); ok = ok && p; return p; };
     PostArgs a{};
     a.pop = d.pop;
     a.up = (const int*)up_d(up, sizeof(int) * nb_trans); a.low = (const int*)up_d(low, sizeof(int) * nb_trans);
@@ -967,21 +980,18 @@ extern "C" rt_status rt_maser_postpass(rt_model* m, const double* pop, int nb_tr
     a.scalars = (double*)out_d(sizeof(double) * 5 * (size_t)nb_trans);
     a.tau_aspect = (double*)out_d(sizeof(double) * (size_t)nb_trans * nb_aspect);
     a.tau_freq = (double*)out_d(sizeof(double) * (size_t)nb_trans * nb_freq);
+    NEED_BUF(ok);
     const int c0 = rt_prof_class(m, "maser_postpass");
     rt_prof_begin(m, c0, m->stream);
     launch_postpass_impl(d, m->stream, a, nb_trans);
     rt_prof_end(m, c0, m->stream);
-    cudaError_t e = cudaStreamSynchronize(m->stream);
-    if (e == cudaSuccess) {
-        if (inv_arr) cudaMemcpy(inv_arr, a.inv_arr, sizeof(double) * (size_t)nb_trans * L, cudaMemcpyDeviceToHost);
-        if (gain_arr) cudaMemcpy(gain_arr, a.gain_arr, sizeof(double) * (size_t)nb_trans * L, cudaMemcpyDeviceToHost);
-        if (scalars) cudaMemcpy(scalars, a.scalars, sizeof(double) * 5 * (size_t)nb_trans, cudaMemcpyDeviceToHost);
-        if (tau_vs_aspect) cudaMemcpy(tau_vs_aspect, a.tau_aspect, sizeof(double) * (size_t)nb_trans * nb_aspect, cudaMemcpyDeviceToHost);
-        if (tau_vs_freq) cudaMemcpy(tau_vs_freq, a.tau_freq, sizeof(double) * (size_t)nb_trans * nb_freq, cudaMemcpyDeviceToHost);
-        e = cudaGetLastError();
-    }
-    for (void* p : tmp) cudaFree(p);
-    CK(e);
+    CK(cudaStreamSynchronize(m->stream));
+    CK(cudaGetLastError());
+    if (inv_arr) CK(cudaMemcpy(inv_arr, a.inv_arr, sizeof(double) * (size_t)nb_trans * L, cudaMemcpyDeviceToHost));
+    if (gain_arr) CK(cudaMemcpy(gain_arr, a.gain_arr, sizeof(double) * (size_t)nb_trans * L, cudaMemcpyDeviceToHost));
+    if (scalars) CK(cudaMemcpy(scalars, a.scalars, sizeof(double) * 5 * (size_t)nb_trans, cudaMemcpyDeviceToHost));
+    if (tau_vs_aspect) CK(cudaMemcpy(tau_vs_aspect, a.tau_aspect, sizeof(double) * (size_t)nb_trans * nb_aspect, cudaMemcpyDeviceToHost));
+    if (tau_vs_freq) CK(cudaMemcpy(tau_vs_freq, a.tau_freq, sizeof(double) * (size_t)nb_trans * nb_freq, cudaMemcpyDeviceToHost));
     return RT_OK;
 }
 
@@ -1003,14 +1013,12 @@ extern "C" rt_status rt_lim_luminosity(rt_model* m, const double* pop, int nb_tr
         if (low[t] < 0 || up[t] >= N || up[t] <= low[t]) { m->last_error = "transition must have up > low"; return RT_ERR_INVALID; }
     rt_status r = rt_set_populations(m, pop);
     if (r != RT_OK) return r;
-    int *up_dev = nullptr, *low_dev = nullptr;
-    double* out_dev = nullptr;
     const size_t nout = (size_t)nb_trans * L * 2;
-    CK(cudaMalloc(&up_dev, sizeof(int) * nb_trans));
-    CK(cudaMalloc(&low_dev, sizeof(int) * nb_trans));
-    CK(cudaMalloc(&out_dev, sizeof(double) * nout));
-    CK(cudaMemcpy(up_dev, up, sizeof(int) * nb_trans, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(low_dev, low, sizeof(int) * nb_trans, cudaMemcpyHostToDevice));
+    DevScratch scratch;
+    int* up_dev = (int*)scratch.get(sizeof(int) * nb_trans, up);
+    int* low_dev = (int*)scratch.get(sizeof(int) * nb_trans, low);
+    double* out_dev = (double*)scratch.get(sizeof(double) * nout);
+    NEED_BUF(up_dev && low_dev && out_dev);
     const int c_l = rt_prof_class(m, "loss_rates");
     m->prof_layers = L;
     rt_prof_begin(m, c_l, m->stream, 0., 0.);
@@ -1020,7 +1028,6 @@ extern "C" rt_status rt_lim_luminosity(rt_model* m, const double* pop, int nb_tr
     CK(cudaGetLastError());
     std::vector<double> rates(nout);
     CK(cudaMemcpy(rates.data(), out_dev, sizeof(double) * nout, cudaMemcpyDeviceToHost));
-    cudaFree(up_dev); cudaFree(low_dev); cudaFree(out_dev);
 
     // the scalar part in the reference's own expression order (maser_luminosity.cpp:78-101)
     const rt_params& pr = d.prm;

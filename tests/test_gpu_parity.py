@@ -205,6 +205,31 @@ def test_error_paths(solver_mod, problems):
     rc = m.L_.rt_cloud_upload(m.h, C.byref(s))
     assert rc == 4
     m.close()
+    m = solver_mod.Model(p)
+    b = m.boundary_layer_populations()
+    with pytest.raises(solver_mod.RtError, match="up > low"):
+        m.lim_luminosity(b, [3], [5])
+    with pytest.raises(solver_mod.RtError):
+        m.intensity_calc(0, p.N, 0, b[0])  # level index out of range
+    assert m.lim_luminosity(b, [], [])["lum"].shape == (0,)  # empty list of transitions is not an error
+    m.close()
+
+
+def test_stacked_clouds_solve_like_separate_models(solver_mod):
+    """Several models per solve (sharding.stack_clouds, bench.py --batch): layers are independent, so stacking changes
+    nothing, bit for bit, including the per-layer iteration counts."""
+    from radiative_transfer_b200 import sharding, synthetic
+    a = synthetic.config_ch3oh(L=3, n_vt=2, n_k=6, n_j=8)
+    b2 = synthetic.config_ch3oh(L=4, n_vt=2, n_k=6, n_j=8, cloud_kw=dict(t_hi=180.0, nh_hi=3e7))
+    s, ranges = sharding.stack_clouds([a, b2])
+    m = solver_mod.Model(s)
+    pop, st = m.calculate_populations()
+    m.close()
+    for q, (lo, hi) in zip((a, b2), ranges):
+        m1 = solver_mod.Model(q)
+        pop1, st1 = m1.calculate_populations()
+        m1.close()
+        assert np.array_equal(pop[lo:hi], pop1) and np.array_equal(st["iters"][lo:hi], st1["iters"])
 
 
 # ---- BASELINE.json full sizes: size-independent properties -------------------------------------------------------
