@@ -38,6 +38,12 @@
 // reduction with ONE barrier; (2) the owners of rows j and p exchange their rows through shared memory, every
 // thread reads the pivot row (broadcast) -- second barrier; (3) rank-1 update in registers.
 // Shared buffers are double-buffered by the parity of j, so two barriers per column suffice.
+// Measured alternative (not kept): ONE barrier per column -- every thread updates column j+1 first, the warp arg-max runs
+// during the rest of the rank-1 update and each warp's local winner publishes its fully updated row as the candidate pivot
+// row, so the "owner publishes the pivot row" round trip disappears.  With four window widths instantiated (no FMA on
+// finished columns, no spills) the kernel grows to 190 KB and stalls on instruction fetch (ncu stall_no_instruction 8.0 per
+// issue); with one 32-wide body it is 1.72 vs 1.68 ms per N = 768 slab-iteration and 0.68 vs 0.57 ms at N = 411: the second
+// barrier is not what bounds the column step.
 // ------------------------------------------------------------------------------------------------------------
 template <int R, int NT>
 __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int nlay_bound)
