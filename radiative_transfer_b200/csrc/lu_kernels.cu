@@ -22,15 +22,30 @@
 #include "rt_internal.h"
 #include <cfloat>
 #include <cstdlib>
+#include <algorithm>
 
 #define PNL_MAXROWS 768 // largest panel height = largest Np
 #ifndef PNL_BIG_R
 #define PNL_BIG_R 3     // rows per thread x threads of the kernel variant for 512 < m <= 768
 #define PNL_BIG_NT 256
 #endif
+#ifndef PNL_DEBUG_JB0
+#define PNL_DEBUG_JB0 0 // development: 32 skips the column loop (times the panel's load / store alone; wrong results)
+#endif
 #ifndef PNL_JB
 #define PNL_JB 8   // columns per unrolled block of the panel's column loop
 #endif
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem));
+}
 
 // ------------------------------------------------------------------------------------------------------------
 // Panel factorisation.  Local row r = t + 256 i (i < R) lives in registers x[i][0..31] of thread t.
@@ -46,10 +61,10 @@
 // barrier is not what bounds the column step.
 // ------------------------------------------------------------------------------------------------------------
 template <int R, int NT>
-__global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int nlay_bound)
+__global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int a0, int a1)
 {
-    const int a = blockIdx.x;
-    if (a >= nlay_bound || a >= *d.n_active) return;
+    const int a = a0 + blockIdx.x;
+    if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
     const int Np = d.Np, ld = d.ld, m = Np - k0;
     double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
@@ -61,10 +76,21 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
     __shared__ int s_pos[64], s_cur[64], s_naff, s_own[2];   // composed permutation (see k_trsm)
     __shared__ short s_slot[NT * R]; // local row -> slot in s_pos, -1 = untouched
 
+    // panel -> staging tile with 8-byte cp.async (the tile's row stride of 33 doubles is not 16-byte aligned): every
+    // thread has all of its m / 8 copies in flight at once.  A plain load loop keeps only the unrolled few rows of each
+    // warp in flight and is latency-bound (~8 GB/s per SM: 20 us of a 55 us panel at m = 768).
+#ifndef PNL_PLAIN_LOAD
+    for (int r = warp; r < m; r += NT / 32) cp_async8(s_tile + r * 33 + lane, A + (size_t)(k0 + r) * ld + k0 + lane);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+#else
     for (int r = warp; r < m; r += NT / 32) s_tile[r * 33 + lane] = A[(size_t)(k0 + r) * ld + k0 + lane];
+#endif
     for (int r = t; r < m; r += NT) s_slot[r] = (short)(r < 32 ? r : -1);
     if (t < 32) { s_pos[t] = t; s_cur[t] = t; }
     if (t == 0) s_naff = 32;
+#ifndef PNL_PLAIN_LOAD
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+#endif
     __syncthreads();
 
     // Rows never move between threads: vp[i] is the CURRENT position of the row held in x[i] (the position the
@@ -84,7 +110,7 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
     }
 
 #pragma unroll 1
-    for (int jb = 0; jb < 32; jb += PNL_JB) {
+    for (int jb = PNL_DEBUG_JB0; jb < 32; jb += PNL_JB) {
 #pragma unroll
         for (int jj = 0; jj < PNL_JB; jj++) {
             const int j = jb + jj;
@@ -204,10 +230,10 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
 // ------------------------------------------------------------------------------------------------------------
 #define TRSM_THREADS 128
 #define TRSM_LDT 34 // even: rows of the transposed triangles stay 16-byte aligned for double2 loads
-__global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, int c0, int mode, int nlay_bound)
+__global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, int c0, int mode, int a0, int a1)
 {
-    const int a = blockIdx.y;
-    if (a >= nlay_bound || a >= *d.n_active) return;
+    const int a = a0 + blockIdx.y;
+    if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
     const int Np = d.Np, ld = d.ld;
     __shared__ __align__(16) double Lt[32 * TRSM_LDT];  // Lt[q][r] = L[r][q] of the panel's unit-lower 32x32 block
@@ -280,21 +306,16 @@ __global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, in
 #define GM_ROWS 128
 #define GM_COLS 64
 #define GM_LDB 68
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
-{
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem));
-}
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
 {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
 template <int K, int ROWS>
-__global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int nlay_bound)
+__global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
-    const int a = blockIdx.z;
-    if (a >= nlay_bound || a >= *d.n_active) return;
+    const int a = a0 + blockIdx.z;
+    if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
     const int Np = d.Np, ld = d.ld;
     constexpr int LDA = K + 4;
@@ -364,10 +385,10 @@ __global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevMode
 // U x = y (y = column Np after the elimination), blocked from the bottom; one CTA per layer.  x -> d.rhs [L][Np].
 // ------------------------------------------------------------------------------------------------------------
 #define BS_THREADS 512
-__global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int nlay_bound)
+__global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int a0, int a1)
 {
-    const int a = blockIdx.x;
-    if (a >= nlay_bound || a >= *d.n_active) return;
+    const int a = a0 + blockIdx.x;
+    if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
     const int Np = d.Np, ld = d.ld, nb = Np / RT_NB;
     extern __shared__ double ys[]; // [Np]: y, progressively reduced to y - U[:, done] x[done]
@@ -429,14 +450,15 @@ __global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int nlay_b
 // ------------------------------------------------------------------------------------------------------------
 // host driver
 // ------------------------------------------------------------------------------------------------------------
-static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, int bound)
+// Every launch works on the slice [a0, a1) of the compacted active list.
+static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, int a0, int a1)
 {
-    const int m = d.Np - k0;
+    const int m = d.Np - k0, n = a1 - a0;
     g_rt_launches++;
     const size_t smem = (size_t)m * 33 * sizeof(double);
-    if (m <= 256) k_panel<1, 256><<<bound, 256, smem, s>>>(d, k0, nleft, bound);
-    else if (m <= 512) k_panel<2, 256><<<bound, 256, smem, s>>>(d, k0, nleft, bound);
-    else k_panel<PNL_BIG_R, PNL_BIG_NT><<<bound, PNL_BIG_NT, smem, s>>>(d, k0, nleft, bound);
+    if (m <= 256) k_panel<1, 256><<<n, 256, smem, s>>>(d, k0, nleft, a0, a1);
+    else if (m <= 512) k_panel<2, 256><<<n, 256, smem, s>>>(d, k0, nleft, a0, a1);
+    else k_panel<PNL_BIG_R, PNL_BIG_NT><<<n, PNL_BIG_NT, smem, s>>>(d, k0, nleft, a0, a1);
 }
 
 // 0: 128x64 tiles, 2 CTAs/SM; 1 (default): 64x64 tiles, 3 CTAs/SM -- 3 % faster at N = 768.  A persistent, cp.async
@@ -444,59 +466,103 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
 // update moves 224 KB per tile through L2 for 4 us of DMMA work, i.e. ~8 TB/s chip-wide -- it is L2-bandwidth-bound,
 // not latency-bound, so deeper pipelining does not help; only a wider outer block (K = 128) would.
 static int g_gemm_mode = 1;
+// Layer groups of one solve (development switch RT_B200_LU_GROUPS).  The layers of a batch are independent, so the
+// active list is cut into G slices whose factorisations run on G streams: while one slice sits in a latency-bound
+// panel (one register-file-filling CTA per SM, 200 layers = 1.35 waves on 148 SMs) the trailing updates of the other
+// slices fill the idle SMs.
+static int g_lu_groups = 2;
+#define LU_GROUP_MIN_LAYERS 48 // below this a slice no longer fills its share of the machine: fewer groups
 
-static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk0, int c0, int c1, int bound)
+static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
-    const dim3 grid((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + GM_ROWS - 1) / GM_ROWS, bound);
+    const int n = a1 - a0;
+    const dim3 grid((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + GM_ROWS - 1) / GM_ROWS, n);
     g_rt_launches++;
-    if (K == 32) k_gemm<32, 128><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
-    else if (g_gemm_mode == 0) k_gemm<64, 128><<<grid, 256, (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
+    if (K == 32) k_gemm<32, 128><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
+    else if (g_gemm_mode == 0) k_gemm<64, 128><<<grid, 256, (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
     else {
-        const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, bound);
-        k_gemm<64, 64><<<g64, 128, (64 * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, bound);
+        const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, n);
+        k_gemm<64, 64><<<g64, 128, (64 * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
     }
 }
 
-void launch_lu_solve(rt_model* m, cudaStream_t s, int bound)
+void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
 {
     const DevModel& d = m->d;
     const int Np = d.Np, ld = d.ld;
     const int c_panel = rt_prof_class(m, "lu_panel"), c_trsm = rt_prof_class(m, "lu_trsm");
     const int c_gemm = rt_prof_class(m, "lu_gemm"), c_back = rt_prof_class(m, "lu_backsolve");
-    auto panel = [&](int k0, int nleft) {
+    // per-class event timing needs the launches of a class back to back on one stream: one group when profiling
+    int G = m->prof_timing ? 1 : std::min(g_lu_groups, std::max(1, bound / LU_GROUP_MIN_LAYERS));
+    G = std::min(G, RT_LU_MAX_GROUPS);
+    if (G > 1 && !m->lu_streams[1]) {
+        for (int g = 1; g < RT_LU_MAX_GROUPS; g++) {
+            if (cudaStreamCreateWithFlags(&m->lu_streams[g], cudaStreamNonBlocking) != cudaSuccess ||
+                cudaEventCreateWithFlags(&m->lu_join[g], cudaEventDisableTiming) != cudaSuccess) { G = 1; break; }
+        }
+        if (G > 1 && cudaEventCreateWithFlags(&m->lu_fork, cudaEventDisableTiming) != cudaSuccess) G = 1;
+    }
+    cudaStream_t st[RT_LU_MAX_GROUPS];
+    int ga0[RT_LU_MAX_GROUPS], ga1[RT_LU_MAX_GROUPS];
+    for (int g = 0; g < G; g++) {
+        st[g] = g == 0 ? s0 : m->lu_streams[g];
+        ga0[g] = (int)((long long)bound * g / G);
+        ga1[g] = (int)((long long)bound * (g + 1) / G);
+    }
+    if (G > 1) {
+        cudaEventRecord(m->lu_fork, s0);
+        for (int g = 1; g < G; g++) cudaStreamWaitEvent(st[g], m->lu_fork, 0);
+    }
+    const int layers_all = m->prof_layers;
+    auto panel = [&](int g, int k0, int nleft) {
         const double mr = Np - k0;
-        rt_prof_begin(m, c_panel, s, 32. * 32. * mr, 16. * 32. * mr);
-        launch_panel(d, s, k0, nleft, bound);
-        rt_prof_end(m, c_panel, s);
+        rt_prof_begin(m, c_panel, st[g], 32. * 32. * mr, 16. * 32. * mr);
+        launch_panel(d, st[g], k0, nleft, ga0[g], ga1[g]);
+        rt_prof_end(m, c_panel, st[g]);
     };
-    auto trsm = [&](int k0, int mode) {
+    auto trsm = [&](int g, int k0, int mode) {
         const int c0 = k0 + 32;
         const double nc = ld - c0;
-        rt_prof_begin(m, c_trsm, s, (mode == 2 ? 3. : 1.) * 32. * 32. * nc, (mode == 2 ? 24. : 16.) * 32. * nc);
+        rt_prof_begin(m, c_trsm, st[g], (mode == 2 ? 3. : 1.) * 32. * 32. * nc, (mode == 2 ? 24. : 16.) * 32. * nc);
         g_rt_launches++;
-        k_trsm<<<dim3((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, bound), TRSM_THREADS, mode == 2 ? 32 * TRSM_THREADS * sizeof(double) : 0, s>>>(d, k0, c0, mode, bound);
-        rt_prof_end(m, c_trsm, s);
+        k_trsm<<<dim3((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]), TRSM_THREADS, mode == 2 ? 32 * TRSM_THREADS * sizeof(double) : 0, st[g]>>>(d, k0, c0, mode, ga0[g], ga1[g]);
+        rt_prof_end(m, c_trsm, st[g]);
     };
-    auto gemm = [&](int K, int i0, int kk0, int c0, int c1) {
+    auto gemm = [&](int g, int K, int i0, int kk0, int c0, int c1) {
         const double mr = Np - i0, nc = c1 - c0;
-        rt_prof_begin(m, c_gemm, s, 2. * K * mr * nc, 16. * mr * nc + 8. * K * (mr + nc));
-        launch_gemm(d, s, K, i0, kk0, c0, c1, bound);
-        rt_prof_end(m, c_gemm, s);
+        rt_prof_begin(m, c_gemm, st[g], 2. * K * mr * nc, 16. * mr * nc + 8. * K * (mr + nc));
+        launch_gemm(d, st[g], K, i0, kk0, c0, c1, ga0[g], ga1[g]);
+        rt_prof_end(m, c_gemm, st[g]);
     };
+    // the groups' launches are issued interleaved, step by step, so that every stream always has work queued
     for (int k0 = 0; k0 < Np; k0 += 64) {
-        panel(k0, 0);
-        trsm(k0, 1);
+        for (int g = 0; g < G; g++) {
+            m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1);
+            panel(g, k0, 0);
+            trsm(g, k0, 1);
+            if (k0 + 32 < Np) gemm(g, 32, k0 + 32, k0, k0 + 32, k0 + 64);
+        }
         if (k0 + 32 < Np) {
-            gemm(32, k0 + 32, k0, k0 + 32, k0 + 64);
-            panel(k0 + 32, 32);
-            trsm(k0 + 32, 2);
-            if (k0 + 64 < Np) gemm(64, k0 + 64, k0, k0 + 64, ld);
+            for (int g = 0; g < G; g++) {
+                m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1);
+                panel(g, k0 + 32, 32);
+                trsm(g, k0 + 32, 2);
+                if (k0 + 64 < Np) gemm(g, 64, k0 + 64, k0, k0 + 64, ld);
+            }
         }
     }
-    rt_prof_begin(m, c_back, s, (double)Np * Np, 4. * Np * Np);
-    g_rt_launches++;
-    k_backsolve<<<bound, BS_THREADS, Np * sizeof(double), s>>>(d, bound);
-    rt_prof_end(m, c_back, s);
+    for (int g = 0; g < G; g++) {
+        m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1);
+        rt_prof_begin(m, c_back, st[g], (double)Np * Np, 4. * Np * Np);
+        g_rt_launches++;
+        k_backsolve<<<ga1[g] - ga0[g], BS_THREADS, Np * sizeof(double), st[g]>>>(d, ga0[g], ga1[g]);
+        rt_prof_end(m, c_back, st[g]);
+    }
+    m->prof_layers = layers_all;
+    for (int g = 1; g < G; g++) {
+        cudaEventRecord(m->lu_join[g], st[g]);
+        cudaStreamWaitEvent(s0, m->lu_join[g], 0);
+    }
 }
 
 int lu_max_np() { return PNL_MAXROWS; }
@@ -514,6 +580,7 @@ cudaError_t lu_kernels_init()
     e = cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * TRSM_THREADS * (int)sizeof(double));
     if (e != cudaSuccess) return e;
     if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switch
+    if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
     e = cudaFuncSetAttribute(k_gemm<64, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (64 * 68 + 64 * GM_LDB) * (int)sizeof(double));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(k_gemm<32, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 36 + 32 * GM_LDB) * (int)sizeof(double));

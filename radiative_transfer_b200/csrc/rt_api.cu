@@ -370,6 +370,11 @@ extern "C" rt_status rt_model_destroy(rt_model* m)
     for (auto& e : m->ev_pool) cudaEventDestroy(e);
     for (auto& e : m->timer_ev) if (e) cudaEventDestroy(e);
     if (m->h_n_active) cudaFreeHost(m->h_n_active);
+    for (int g = 1; g < RT_LU_MAX_GROUPS; g++) {
+        if (m->lu_streams[g]) cudaStreamDestroy(m->lu_streams[g]);
+        if (m->lu_join[g]) cudaEventDestroy(m->lu_join[g]);
+    }
+    if (m->lu_fork) cudaEventDestroy(m->lu_fork);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
     return RT_OK;

@@ -23,6 +23,7 @@
 #define RT_MAX_TABLES 16
 #define RT_MAX_DUST 8
 #define RT_NB 32 // LU panel width == padding granularity
+#define RT_LU_MAX_GROUPS 8 // streams one batched LU may be spread over (lu_kernels.cu: launch_lu_solve)
 #define RT_AFF_STRIDE 132 // {n_aff, pad, pad, pad, pos[64], cur[64]}
 
 struct DevTable {            // one collision_data, transposed to [jmax][imax] so one layer's T-row is contiguous
@@ -83,6 +84,8 @@ struct rt_model {
     size_t cloud_slot = 0;
     std::vector<std::vector<double>> h_tgrid; // host copy of the collision tables' temperature grids (set_gas_param)
     cudaStream_t stream = nullptr;
+    cudaStream_t lu_streams[RT_LU_MAX_GROUPS] = {};  // side streams of the grouped LU ([0] unused: group 0 runs on `stream`)
+    cudaEvent_t lu_fork = nullptr, lu_join[RT_LU_MAX_GROUPS] = {};
     int* h_n_active = nullptr;     // pinned
     bool has_cloud = false;
     bool use_fused = true;         // persistent one-CTA-per-layer solver when the matrix fits in shared memory
