@@ -60,6 +60,7 @@ __device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
 // issue); with one 32-wide body it is 1.72 vs 1.68 ms per N = 768 slab-iteration and 0.68 vs 0.57 ms at N = 411: the second
 // barrier is not what bounds the column step.
 // ------------------------------------------------------------------------------------------------------------
+#ifdef PNL_V1
 template <int R, int NT>
 __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int a0, int a1)
 {
@@ -218,6 +219,231 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
         }
     }
 }
+
+#else // !PNL_V1
+// ------------------------------------------------------------------------------------------------------------
+// Panel factorisation, blocked inside the panel (default).  The column step of the kernel above is bound by the
+// instructions a warp issues between two barriers (ncu: ~500 cycles of fixed latency + ~3.4 cycles per instruction
+// with 2 warps per scheduler; 400 instructions per column at 3 rows per thread, of which 82 DFMA on the 32-wide row
+// and 48 LDS of the pivot row).  Here the 32 columns are factored as four SUB-PANELS of 8 columns: inside a
+// sub-panel a column step touches only the 8 sub-panel columns of every row (<= 7 DFMA per row, 4 LDS, the pivot
+// row published as 8 doubles); the 24 (16, 8) columns to the right are updated once per sub-panel by a dense rank-8
+// update from registers -- no barrier, no pivot search in between:
+//     U12 = L11^-1 A12      24 threads, one column each (the 8 pivot rows publish their trailing parts)
+//     A22 -= L21 U12        every thread on its own rows, multipliers L21 = its x[i][0..7]
+// For every matrix entry this is the same sequence of fused multiply-adds, in the same order, as the eager rank-1
+// updates: the factors are bitwise identical to the unblocked kernel's.
+// The window of live columns is shifted left by 8 registers after every sub-panel (register indices must be
+// static; one code body serves the four sub-panels), finished entries go to the staging tile.
+// ------------------------------------------------------------------------------------------------------------
+template <int R, int NC>
+__device__ __forceinline__ void panel_rank8(double (&x)[R][32], const bool (&live)[R], const double* __restrict__ u12 /*[8][24]*/)
+{
+#pragma unroll
+    for (int c = 0; c < NC; c += 2) {
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const double2 u = *reinterpret_cast<const double2*>(u12 + q * 24 + c);
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                if (live[i]) {
+                    x[i][8 + c] -= x[i][q] * u.x;
+                    x[i][9 + c] -= x[i][q] * u.y;
+                }
+            }
+        }
+    }
+}
+
+template <int R, int NT>
+__global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int a0, int a1)
+{
+    const int a = a0 + blockIdx.x;
+    if (a >= a1 || a >= *d.n_active) return;
+    const int lay = d.active[a];
+    const int Np = d.Np, ld = d.ld, m = Np - k0;
+    double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+
+    extern __shared__ double s_tile[]; // [m][33]: coalesced staging of the panel on the way in and out
+    __shared__ unsigned long long s_key[2][NT / 32];
+    __shared__ __align__(16) double s_prow[2][8];  // sub-panel columns of the pivot row
+    __shared__ __align__(16) double s_l11[8][8];   // sub-panel columns of the 8 pivot rows (their multipliers: unit-lower L11)
+    __shared__ __align__(16) double s_a12[8][24];  // trailing columns of the 8 pivot rows, overwritten by U12
+    __shared__ int s_ownrow[8];                    // local row (t + NT i) that holds pivot q of the sub-panel
+    __shared__ int s_pos[64], s_cur[64], s_naff;   // composed permutation (see k_trsm)
+    __shared__ short s_slot[NT * R]; // local row -> slot in s_pos, -1 = untouched
+
+    // panel -> staging tile with 8-byte cp.async (the tile's row stride of 33 doubles is not 16-byte aligned): every
+    // thread has all of its m / 8 copies in flight at once
+    for (int r = warp; r < m; r += NT / 32) cp_async8(s_tile + r * 33 + lane, A + (size_t)(k0 + r) * ld + k0 + lane);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (int r = t; r < m; r += NT) s_slot[r] = (short)(r < 32 ? r : -1);
+    if (t < 32) { s_pos[t] = t; s_cur[t] = t; }
+    if (t == 0) s_naff = 32;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+
+    // Rows never move between threads: vp[i] is the CURRENT position of the row held in x[i] (the position the
+    // scalar algorithm's interchanges would have put it at), -1 for padding slots.  x[i][c] holds column jb + c.
+    double x[R][32];
+    int vp[R];
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        const int r = t + NT * i;
+        vp[i] = r < m ? r : -1;
+#pragma unroll
+        for (int c = 0; c < 32; c++) x[i][c] = r < m ? s_tile[r * 33 + c] : 0.;
+    }
+
+#pragma unroll 1
+    for (int jb = PNL_DEBUG_JB0; jb < 32; jb += 8) {
+#pragma unroll
+        for (int jj = 0; jj < 8; jj++) {
+            const int j = jb + jj;
+            const int buf = jj & 1;
+            // ---- (1) pivot search over the rows at positions >= j.  64-bit keys: |a| with its low 10 bits replaced by
+            // 1023 - (position - j): the larger value wins, values equal in their top 54 bits (relative difference
+            // < 2e-13, immaterial for the pivot choice) count as ties -> smallest position, like the scalar loop.
+            // Warp arg-max = two REDUX instructions instead of five shuffle rounds.
+            unsigned long long key = 0ull;
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                if (vp[i] >= j) {
+                    const unsigned long long kk = ((unsigned long long)__double_as_longlong(fabs(x[i][jj])) & ~0x3FFull)
+                                                  | (unsigned long long)(1023 - (vp[i] - j));
+                    key = kk > key ? kk : key;
+                }
+            }
+            {
+                const unsigned hi = (unsigned)(key >> 32);
+                const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+                const unsigned lo = hi == mhi ? (unsigned)key : 0u;
+                const unsigned mlo = __reduce_max_sync(0xffffffffu, lo);
+                if (lane == 0) s_key[buf][warp] = ((unsigned long long)mhi << 32) | mlo;
+            }
+            __syncthreads();
+            key = s_key[buf][0];
+#pragma unroll
+            for (int w = 1; w < NT / 32; w++) { const unsigned long long kk = s_key[buf][w]; key = kk > key ? kk : key; }
+            const int p = j + 1023 - (int)(key & 0x3FFull);
+            // ---- (2) interchange of positions j <-> p: the pivot row publishes its sub-panel columns, nothing else moves
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                if (vp[i] == p) {
+                    double2* pr = reinterpret_cast<double2*>(s_prow[buf]);
+#pragma unroll
+                    for (int c = 0; c < 4; c++) pr[c] = make_double2(x[i][2 * c], x[i][2 * c + 1]);
+                    s_ownrow[jj] = t + NT * i;
+                    vp[i] = j;
+                }
+                else if (vp[i] == j) vp[i] = p;
+            }
+            if (t == 0 && p != j) {
+                // bookkeeping of the composed permutation: s_cur[slot] = slot of the ORIGINAL row now at s_pos[slot]
+                int sp = s_slot[p];
+                if (sp < 0) { sp = s_naff++; s_pos[sp] = p; s_cur[sp] = sp; s_slot[p] = (short)sp; }
+                const int tmp = s_cur[j]; s_cur[j] = s_cur[sp]; s_cur[sp] = tmp;
+            }
+            __syncthreads();
+            // ---- (3) rank-1 update of the sub-panel columns of the rows below j; the multiplier stays in the register
+            const double piv = s_prow[buf][jj];
+            const double rp = piv != 0. ? __drcp_rn(piv) : 0.; // == 1. / piv (correctly rounded); zero pivot: column left alone
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                if (vp[i] > j) {
+                    const double l = x[i][jj] * rp;
+                    x[i][jj] = l;
+#pragma unroll
+                    for (int c = jj + 1; c < 8; c++) x[i][c] -= l * s_prow[buf][c];
+                }
+            }
+        }
+        // ---- (4) the columns right of the sub-panel: U12 = L11^-1 A12, A22 -= L21 U12
+        const int ntr = 24 - jb; // live columns right of the sub-panel (window columns 8 .. 8 + ntr)
+        if (ntr > 0) {
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                const int q = vp[i] - jb;
+                if (q >= 0 && q < 8) {
+                    double2* l11 = reinterpret_cast<double2*>(s_l11[q]);
+#pragma unroll
+                    for (int c = 0; c < 4; c++) l11[c] = make_double2(x[i][2 * c], x[i][2 * c + 1]);
+                    double2* a12 = reinterpret_cast<double2*>(s_a12[q]);
+#pragma unroll
+                    for (int c = 0; c < 12; c++) a12[c] = make_double2(x[i][8 + 2 * c], x[i][9 + 2 * c]);
+                }
+            }
+            __syncthreads();
+            if (t < ntr) {
+                double u[8];
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    double v = s_a12[q][t];
+#pragma unroll
+                    for (int r = 0; r < q; r++) v -= s_l11[q][r] * u[r];
+                    u[q] = v;
+                }
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    s_a12[q][t] = u[q];
+                    s_tile[s_ownrow[q] * 33 + jb + 8 + t] = u[q]; // final U entries of the pivot rows
+                }
+            }
+            __syncthreads();
+            bool live[R];
+#pragma unroll
+            for (int i = 0; i < R; i++) live[i] = vp[i] >= jb + 8;
+            if (jb == 0) panel_rank8<R, 24>(x, live, &s_a12[0][0]);
+            else if (jb == 8) panel_rank8<R, 16>(x, live, &s_a12[0][0]);
+            else panel_rank8<R, 8>(x, live, &s_a12[0][0]);
+        }
+        // ---- (5) finished sub-panel columns (multipliers; U entries of the rows that became pivots here) -> staging tile;
+        // rows that became pivots in an EARLIER sub-panel are complete there already (their registers are dead)
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            if (vp[i] >= jb) {
+                double* dst = s_tile + (t + NT * i) * 33 + jb;
+#pragma unroll
+                for (int c = 0; c < 8; c++) dst[c] = x[i][c];
+            }
+#pragma unroll
+            for (int c = 0; c < 24; c++) x[i][c] = x[i][c + 8];
+#pragma unroll
+            for (int c = 24; c < 32; c++) x[i][c] = 0.;
+        }
+    }
+
+    // ---- write the factored panel back: row at final position vp <- staging-tile row of its owner (coalesced)
+    __shared__ short s_owner[NT * R];
+#pragma unroll
+    for (int i = 0; i < R; i++)
+        if (vp[i] >= 0) s_owner[vp[i]] = (short)(t + NT * i);
+    __syncthreads();
+    for (int r = warp; r < m; r += NT / 32) A[(size_t)(k0 + r) * ld + k0 + lane] = s_tile[s_owner[r] * 33 + lane];
+    const int naff = s_naff;
+    int* aff = d.lu_aff + ((size_t)lay * (Np / RT_NB) + k0 / RT_NB) * RT_AFF_STRIDE;
+    if (t == 0) aff[0] = naff;
+    if (t < 64) { aff[4 + t] = t < naff ? s_pos[t] : 0; aff[68 + t] = t < naff ? s_cur[t] : 0; }
+    // ---- LAPACK-style interchange of the `nleft` columns left of the panel (the L block of the first panel of
+    // this outer block): gather every affected row, barrier, scatter
+    if (nleft > 0) {
+        double v[8];
+        const int nel = naff * nleft; // <= 64 * 32
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int e = t + NT * q;
+            if (e < nel) { const int s = e / nleft, c = e - s * nleft; v[q] = A[(size_t)(k0 + s_pos[s_cur[s]]) * ld + k0 - nleft + c]; }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int e = t + NT * q;
+            if (e < nel) { const int s = e / nleft, c = e - s * nleft; if (s_cur[s] != s) A[(size_t)(k0 + s_pos[s]) * ld + k0 - nleft + c] = v[q]; }
+        }
+    }
+}
+#endif // PNL_V1
 
 // ------------------------------------------------------------------------------------------------------------
 // Row permutation + triangular solve for the columns right of a panel.  One thread per column, 128 columns per
