@@ -236,8 +236,9 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
 // The window of live columns is shifted left by 8 registers after every sub-panel (register indices must be
 // static; one code body serves the four sub-panels), finished entries go to the staging tile.
 // ------------------------------------------------------------------------------------------------------------
+// Rows that are pivots already (and padding slots) are updated too: their registers are dead, nobody reads them again.
 template <int R, int NC>
-__device__ __forceinline__ void panel_rank8(double (&x)[R][32], const bool (&live)[R], const double* __restrict__ u12 /*[8][24]*/)
+__device__ __forceinline__ void panel_rank8(double (&x)[R][32], const double* __restrict__ u12 /*[8][24]*/)
 {
 #pragma unroll
     for (int c = 0; c < NC; c += 2) {
@@ -246,10 +247,8 @@ __device__ __forceinline__ void panel_rank8(double (&x)[R][32], const bool (&liv
             const double2 u = *reinterpret_cast<const double2*>(u12 + q * 24 + c);
 #pragma unroll
             for (int i = 0; i < R; i++) {
-                if (live[i]) {
-                    x[i][8 + c] -= x[i][q] * u.x;
-                    x[i][9 + c] -= x[i][q] * u.y;
-                }
+                x[i][8 + c] -= x[i][q] * u.x;
+                x[i][9 + c] -= x[i][q] * u.y;
             }
         }
     }
@@ -276,12 +275,16 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
 
     // panel -> staging tile with 8-byte cp.async (the tile's row stride of 33 doubles is not 16-byte aligned): every
     // thread has all of its m / 8 copies in flight at once
+#ifndef PNL_DIRECT_LOAD
     for (int r = warp; r < m; r += NT / 32) cp_async8(s_tile + r * 33 + lane, A + (size_t)(k0 + r) * ld + k0 + lane);
     asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
     for (int r = t; r < m; r += NT) s_slot[r] = (short)(r < 32 ? r : -1);
     if (t < 32) { s_pos[t] = t; s_cur[t] = t; }
     if (t == 0) s_naff = 32;
+#ifndef PNL_DIRECT_LOAD
     asm volatile("cp.async.wait_group 0;" ::: "memory");
+#endif
     __syncthreads();
 
     // Rows never move between threads: vp[i] is the CURRENT position of the row held in x[i] (the position the
@@ -292,8 +295,19 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
     for (int i = 0; i < R; i++) {
         const int r = t + NT * i;
         vp[i] = r < m ? r : -1;
+#ifdef PNL_DIRECT_LOAD
+        // every thread reads its own rows (256 contiguous bytes each) straight into registers: 16 independent 16-byte loads
+        // per row in flight, no shared-memory round trip
+        const double2* src = reinterpret_cast<const double2*>(A + (size_t)(k0 + (r < m ? r : 0)) * ld + k0);
+#pragma unroll
+        for (int c = 0; c < 16; c++) {
+            const double2 v = r < m ? src[c] : make_double2(0., 0.);
+            x[i][2 * c] = v.x; x[i][2 * c + 1] = v.y;
+        }
+#else
 #pragma unroll
         for (int c = 0; c < 32; c++) x[i][c] = r < m ? s_tile[r * 33 + c] : 0.;
+#endif
     }
 
 #pragma unroll 1
@@ -391,12 +405,9 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
                 }
             }
             __syncthreads();
-            bool live[R];
-#pragma unroll
-            for (int i = 0; i < R; i++) live[i] = vp[i] >= jb + 8;
-            if (jb == 0) panel_rank8<R, 24>(x, live, &s_a12[0][0]);
-            else if (jb == 8) panel_rank8<R, 16>(x, live, &s_a12[0][0]);
-            else panel_rank8<R, 8>(x, live, &s_a12[0][0]);
+            if (jb == 0) panel_rank8<R, 24>(x, &s_a12[0][0]);
+            else if (jb == 8) panel_rank8<R, 16>(x, &s_a12[0][0]);
+            else panel_rank8<R, 8>(x, &s_a12[0][0]);
         }
         // ---- (5) finished sub-panel columns (multipliers; U entries of the rows that became pivots here) -> staging tile;
         // rows that became pivots in an EARLIER sub-panel are complete there already (their registers are dead)
