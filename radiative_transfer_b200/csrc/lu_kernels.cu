@@ -41,6 +41,10 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem));
 }
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
 __device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
 {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -467,6 +471,7 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
 // ------------------------------------------------------------------------------------------------------------
 #define TRSM_THREADS 128
 #define TRSM_LDT 34 // even: rows of the transposed triangles stay 16-byte aligned for double2 loads
+#define TRSM_LDU (TRSM_THREADS + 4) // row stride of s_u: = 4 (mod 16) doubles -> conflict-free DMMA fragment loads
 __global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, int c0, int mode, int a0, int a1)
 {
     const int a = a0 + blockIdx.y;
@@ -476,7 +481,7 @@ __global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, in
     __shared__ __align__(16) double Lt[32 * TRSM_LDT];  // Lt[q][r] = L[r][q] of the panel's unit-lower 32x32 block
     __shared__ __align__(16) double Llt[32 * TRSM_LDT]; // mode 2: Llt[q][r] = A[k0+r][k0-32+q]
     __shared__ int s_pos[64], s_cur[64];
-    extern __shared__ double s_u[]; // mode 2: [32][TRSM_THREADS] rows k0-32..k0-1 (U1) of this column tile
+    extern __shared__ __align__(16) double s_u[]; // mode 2: [32][TRSM_LDU] rows k0-32..k0-1 (U1) of this column tile
     double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
     const int* aff = d.lu_aff + ((size_t)lay * (Np / RT_NB) + k0 / RT_NB) * RT_AFF_STRIDE;
     const int naff = aff[0];
@@ -496,17 +501,18 @@ __global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, in
     for (int r = 0; r < 32; r++) x[r] = A[(size_t)(k0 + s_pos[s_cur[r]]) * ld + c];
     if (mode == 2) {
 #pragma unroll
-        for (int q = 0; q < 32; q++) s_u[q * TRSM_THREADS + tid] = A[(size_t)(k0 - 32 + q) * ld + c];
+        for (int q = 0; q < 32; q++) s_u[q * TRSM_LDU + tid] = A[(size_t)(k0 - 32 + q) * ld + c];
     }
     // rows displaced below the block receive ORIGINAL top rows (still untouched in memory: they are rewritten last)
     for (int s = 32; s < naff; s++)
         if (s_cur[s] != s) A[(size_t)(k0 + s_pos[s]) * ld + c] = A[(size_t)(k0 + s_pos[s_cur[s]]) * ld + c];
     if (mode == 2) {
+#ifdef TRSM_FMA_LEFT
         // x -= Lleft * u: column sweep, 32 independent accumulators per step
 #pragma unroll
         for (int q = 0; q < 32; q++) {
             const double2* lq = reinterpret_cast<const double2*>(Llt + q * TRSM_LDT);
-            const double uq = s_u[q * TRSM_THREADS + tid]; // written by this thread: no barrier needed
+            const double uq = s_u[q * TRSM_LDU + tid]; // written by this thread: no barrier needed
 #pragma unroll
             for (int r2 = 0; r2 < 16; r2++) {
                 const double2 l = lq[r2];
@@ -514,6 +520,45 @@ __global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, in
                 x[2 * r2 + 1] -= l.y * uq;
             }
         }
+#else
+        // x -= Lleft * u on the FP64 tensor cores: per warp a (32 x 32) x (32 x 32) product P = Lleft * U1 of the warp's own
+        // 32 columns (staged by its own lanes: only warp-level synchronisation), 128 DMMA + 64 fragment loads instead of
+        // 1024 DFMA + 544 shared-memory loads per thread (the scalar sweep is bound by the shared-memory pipe).  P goes back
+        // through the warp's slice of s_u to the one-column-per-thread layout of the forward substitution.
+        __syncwarp();
+        const int fr = lane >> 2, fk = lane & 3;
+        const double* Aw = Llt + fk * TRSM_LDT + fr;
+        double* Bw = s_u + fk * TRSM_LDU + warp * 32;
+#pragma unroll
+        for (int h = 0; h < 2; h++) { // two halves of 16 columns: 16 accumulators beside the 32 entries of x
+            double acc[4][2][2];
+#pragma unroll
+            for (int ti = 0; ti < 4; ti++)
+#pragma unroll
+                for (int tj = 0; tj < 2; tj++) acc[ti][tj][0] = acc[ti][tj][1] = 0.;
+#pragma unroll
+            for (int k4 = 0; k4 < 8; k4++) {
+                double af[4], bf[2];
+#pragma unroll
+                for (int ti = 0; ti < 4; ti++) af[ti] = Aw[4 * k4 * TRSM_LDT + ti * 8];
+#pragma unroll
+                for (int tj = 0; tj < 2; tj++) bf[tj] = Bw[4 * k4 * TRSM_LDU + h * 16 + tj * 8 + fr];
+#pragma unroll
+                for (int ti = 0; ti < 4; ti++)
+#pragma unroll
+                    for (int tj = 0; tj < 2; tj++) dmma884(acc[ti][tj][0], acc[ti][tj][1], af[ti], bf[tj]);
+            }
+            __syncwarp(); // every lane has read its fragments of these 16 columns: P may overwrite them
+#pragma unroll
+            for (int ti = 0; ti < 4; ti++)
+#pragma unroll
+                for (int tj = 0; tj < 2; tj++)
+                    *reinterpret_cast<double2*>(s_u + (ti * 8 + fr) * TRSM_LDU + warp * 32 + h * 16 + tj * 8 + 2 * fk) = make_double2(acc[ti][tj][0], acc[ti][tj][1]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < 32; r++) x[r] -= s_u[r * TRSM_LDU + tid];
+#endif
     }
     // forward substitution, right-looking: after x[q] is final, every x[r], r > q, is updated independently
 #pragma unroll
@@ -543,10 +588,6 @@ __global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, in
 #define GM_ROWS 128
 #define GM_COLS 64
 #define GM_LDB 68
-__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
-{
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
 
 template <int K, int ROWS>
 __global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
@@ -635,8 +676,21 @@ __global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int a0, in
     double* __restrict__ xo = d.rhs + (size_t)lay * Np;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int r = tid; r < Np; r += BS_THREADS) ys[r] = A[(size_t)r * ld + Np];
+    // The update of block kb reads the column panel U[0 .. r0)[r0 .. r0 + 32) right after the triangular solve: a dependent
+    // chain of (global-load latency + solve) per block.  The addresses do not depend on x, so the panel (and the diagonal
+    // block) of block kb - 1 is prefetched one block ahead, two 128-byte lines per row.
+    auto prefetch_block = [&](int kbp) {
+        if (kbp < 0) return;
+        const int rp = kbp * RT_NB;
+        for (int e = tid; e < 2 * (rp + 32); e += BS_THREADS) {
+            const double* q = A + (size_t)(e >> 1) * ld + rp + 16 * (e & 1);
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(q));
+        }
+    };
+    prefetch_block(nb - 1);
     for (int kb = nb - 1; kb >= 0; kb--) {
         const int r0 = kb * RT_NB;
+        prefetch_block(kb - 1);
         for (int rr = warp; rr < 32; rr += BS_THREADS / 32) Us[rr][lane] = A[(size_t)(r0 + rr) * ld + r0 + lane];
         __syncthreads();
         if (warp == 0) {
@@ -762,7 +816,7 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
         const double nc = ld - c0;
         rt_prof_begin(m, c_trsm, st[g], (mode == 2 ? 3. : 1.) * 32. * 32. * nc, (mode == 2 ? 24. : 16.) * 32. * nc);
         g_rt_launches++;
-        k_trsm<<<dim3((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]), TRSM_THREADS, mode == 2 ? 32 * TRSM_THREADS * sizeof(double) : 0, st[g]>>>(d, k0, c0, mode, ga0[g], ga1[g]);
+        k_trsm<<<dim3((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]), TRSM_THREADS, mode == 2 ? 32 * TRSM_LDU * sizeof(double) : 0, st[g]>>>(d, k0, c0, mode, ga0[g], ga1[g]);
         rt_prof_end(m, c_trsm, st[g]);
     };
     auto gemm = [&](int g, int K, int i0, int kk0, int c0, int c1) {
@@ -814,7 +868,7 @@ cudaError_t lu_kernels_init()
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(k_gemm<64, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double));
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * TRSM_THREADS * (int)sizeof(double));
+    e = cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * TRSM_LDU * (int)sizeof(double));
     if (e != cudaSuccess) return e;
     if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switch
     if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
