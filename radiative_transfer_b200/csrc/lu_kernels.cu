@@ -52,184 +52,17 @@ __device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// Panel factorisation.  Local row r = t + 256 i (i < R) lives in registers x[i][0..31] of thread t.
-// Per column j: (1) arg-max |x[.][j]| over rows >= j (ties -> smallest row, like the scalar loop), two-stage
-// reduction with ONE barrier; (2) the owners of rows j and p exchange their rows through shared memory, every
-// thread reads the pivot row (broadcast) -- second barrier; (3) rank-1 update in registers.
-// Shared buffers are double-buffered by the parity of j, so two barriers per column suffice.
-// Measured alternative (not kept): ONE barrier per column -- every thread updates column j+1 first, the warp arg-max runs
-// during the rest of the rank-1 update and each warp's local winner publishes its fully updated row as the candidate pivot
-// row, so the "owner publishes the pivot row" round trip disappears.  With four window widths instantiated (no FMA on
-// finished columns, no spills) the kernel grows to 190 KB and stalls on instruction fetch (ncu stall_no_instruction 8.0 per
-// issue); with one 32-wide body it is 1.72 vs 1.68 ms per N = 768 slab-iteration and 0.68 vs 0.57 ms at N = 411: the second
-// barrier is not what bounds the column step.
-// ------------------------------------------------------------------------------------------------------------
-#ifdef PNL_V1
-template <int R, int NT>
-__global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int a0, int a1)
-{
-    const int a = a0 + blockIdx.x;
-    if (a >= a1 || a >= *d.n_active) return;
-    const int lay = d.active[a];
-    const int Np = d.Np, ld = d.ld, m = Np - k0;
-    double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
-    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-
-    extern __shared__ double s_tile[]; // [m][33]: coalesced staging of the panel on the way in and out
-    __shared__ unsigned long long s_key[2][NT / 32];
-    __shared__ __align__(16) double s_prow[2][32]; // pivot row (all 32 columns)
-    __shared__ int s_pos[64], s_cur[64], s_naff, s_own[2];   // composed permutation (see k_trsm)
-    __shared__ short s_slot[NT * R]; // local row -> slot in s_pos, -1 = untouched
-
-    // panel -> staging tile with 8-byte cp.async (the tile's row stride of 33 doubles is not 16-byte aligned): every
-    // thread has all of its m / 8 copies in flight at once.  A plain load loop keeps only the unrolled few rows of each
-    // warp in flight and is latency-bound (~8 GB/s per SM: 20 us of a 55 us panel at m = 768).
-#ifndef PNL_PLAIN_LOAD
-    for (int r = warp; r < m; r += NT / 32) cp_async8(s_tile + r * 33 + lane, A + (size_t)(k0 + r) * ld + k0 + lane);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-#else
-    for (int r = warp; r < m; r += NT / 32) s_tile[r * 33 + lane] = A[(size_t)(k0 + r) * ld + k0 + lane];
-#endif
-    for (int r = t; r < m; r += NT) s_slot[r] = (short)(r < 32 ? r : -1);
-    if (t < 32) { s_pos[t] = t; s_cur[t] = t; }
-    if (t == 0) s_naff = 32;
-#ifndef PNL_PLAIN_LOAD
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-#endif
-    __syncthreads();
-
-    // Rows never move between threads: vp[i] is the CURRENT position of the row held in x[i] (the position the
-    // scalar algorithm's interchanges would have put it at), -1 for padding slots.  x[i][c] holds column jb + c of
-    // the row, jb = first column of the current block of PNL_JB columns: the column loop is unrolled over one
-    // block only (register indices must be static; fully unrolling 32 columns gives 430 KB of straight-line code
-    // that stalls on instruction fetch) and the registers are shifted left by PNL_JB after every block.
-    // Finished entries (multipliers, pivot rows) go to the staging tile row of the thread's ORIGINAL row.
-    double x[R][32];
-    int vp[R];
-#pragma unroll
-    for (int i = 0; i < R; i++) {
-        const int r = t + NT * i;
-        vp[i] = r < m ? r : -1;
-#pragma unroll
-        for (int c = 0; c < 32; c++) x[i][c] = r < m ? s_tile[r * 33 + c] : 0.;
-    }
-
-#pragma unroll 1
-    for (int jb = PNL_DEBUG_JB0; jb < 32; jb += PNL_JB) {
-#pragma unroll
-        for (int jj = 0; jj < PNL_JB; jj++) {
-            const int j = jb + jj;
-            const int buf = jj & 1;
-            // ---- (1) pivot search over the rows at positions >= j.  64-bit keys: |a| with its low 10 bits replaced by
-            // 1023 - (position - j): the larger value wins, values equal in their top 54 bits (relative difference
-            // < 2e-13, immaterial for the pivot choice) count as ties -> smallest position, like the scalar loop.
-            // Warp arg-max = two REDUX instructions instead of five shuffle rounds.
-            unsigned long long key = 0ull;
-#pragma unroll
-            for (int i = 0; i < R; i++) {
-                if (vp[i] >= j) {
-                    const unsigned long long kk = ((unsigned long long)__double_as_longlong(fabs(x[i][jj])) & ~0x3FFull)
-                                                  | (unsigned long long)(1023 - (vp[i] - j));
-                    key = kk > key ? kk : key;
-                }
-            }
-            {
-                const unsigned hi = (unsigned)(key >> 32);
-                const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
-                const unsigned lo = hi == mhi ? (unsigned)key : 0u;
-                const unsigned mlo = __reduce_max_sync(0xffffffffu, lo);
-                if (lane == 0) s_key[buf][warp] = ((unsigned long long)mhi << 32) | mlo;
-            }
-            __syncthreads();
-            key = s_key[buf][0];
-#pragma unroll
-            for (int w = 1; w < NT / 32; w++) { const unsigned long long kk = s_key[buf][w]; key = kk > key ? kk : key; }
-            const int p = j + 1023 - (int)(key & 0x3FFull);
-            // ---- (2) interchange of positions j <-> p: the pivot row is published, nothing else moves
-#pragma unroll
-            for (int i = 0; i < R; i++) {
-                if (vp[i] == p) {
-                    double2* pr = reinterpret_cast<double2*>(s_prow[buf]);
-#pragma unroll
-                    for (int c = 0; c < 16; c++) pr[c] = make_double2(x[i][2 * c], x[i][2 * c + 1]);
-                    s_own[buf] = t + NT * i;
-                    vp[i] = j;
-                }
-                else if (vp[i] == j) vp[i] = p;
-            }
-            if (t == 0 && p != j) {
-                // bookkeeping of the composed permutation: s_cur[slot] = slot of the ORIGINAL row now at s_pos[slot]
-                int sp = s_slot[p];
-                if (sp < 0) { sp = s_naff++; s_pos[sp] = p; s_cur[sp] = sp; s_slot[p] = (short)sp; }
-                const int tmp = s_cur[j]; s_cur[j] = s_cur[sp]; s_cur[sp] = tmp;
-            }
-            __syncthreads();
-            // U part of the pivot row is final: into the owner's staging-tile row (columns j..31)
-            if (t >= jj && jb + t < 32) s_tile[s_own[buf] * 33 + jb + t] = s_prow[buf][t];
-            // ---- (3) rank-1 update of the rows below j
-            const double piv = s_prow[buf][jj];
-            const double rp = __drcp_rn(piv); // == 1. / piv (correctly rounded), shorter dependency chain
-#pragma unroll
-            for (int i = 0; i < R; i++) {
-                if (vp[i] > j) {
-                    double l = x[i][jj];
-                    if (piv != 0.) {
-                        l *= rp;
-                        if (l != 0.) {
-#pragma unroll
-                            for (int c = jj + 1; c < 32; c++) x[i][c] -= l * s_prow[buf][c];
-                        }
-                    }
-                    s_tile[(t + NT * i) * 33 + j] = l; // multiplier (or the untouched entry if piv == 0)
-                }
-            }
-        }
-        // shift the live columns to the front
-#pragma unroll
-        for (int i = 0; i < R; i++) {
-#pragma unroll
-            for (int c = 0; c < 32 - PNL_JB; c++) x[i][c] = x[i][c + PNL_JB];
-#pragma unroll
-            for (int c = 32 - PNL_JB; c < 32; c++) x[i][c] = 0.;
-        }
-    }
-
-    // ---- write the factored panel back: row at final position vp <- staging-tile row of its owner (coalesced)
-    __shared__ short s_owner[NT * R];
-#pragma unroll
-    for (int i = 0; i < R; i++)
-        if (vp[i] >= 0) s_owner[vp[i]] = (short)(t + NT * i);
-    __syncthreads();
-    for (int r = warp; r < m; r += NT / 32) A[(size_t)(k0 + r) * ld + k0 + lane] = s_tile[s_owner[r] * 33 + lane];
-    const int naff = s_naff;
-    int* aff = d.lu_aff + ((size_t)lay * (Np / RT_NB) + k0 / RT_NB) * RT_AFF_STRIDE;
-    if (t == 0) aff[0] = naff;
-    if (t < 64) { aff[4 + t] = t < naff ? s_pos[t] : 0; aff[68 + t] = t < naff ? s_cur[t] : 0; }
-    // ---- LAPACK-style interchange of the `nleft` columns left of the panel (the L block of the first panel of
-    // this outer block): gather every affected row, barrier, scatter
-    if (nleft > 0) {
-        double v[8];
-        const int nel = naff * nleft; // <= 64 * 32
-#pragma unroll
-        for (int q = 0; q < 8; q++) {
-            const int e = t + NT * q;
-            if (e < nel) { const int s = e / nleft, c = e - s * nleft; v[q] = A[(size_t)(k0 + s_pos[s_cur[s]]) * ld + k0 - nleft + c]; }
-        }
-        __syncthreads();
-#pragma unroll
-        for (int q = 0; q < 8; q++) {
-            const int e = t + NT * q;
-            if (e < nel) { const int s = e / nleft, c = e - s * nleft; if (s_cur[s] != s) A[(size_t)(k0 + s_pos[s]) * ld + k0 - nleft + c] = v[q]; }
-        }
-    }
-}
-
-#else // !PNL_V1
-// ------------------------------------------------------------------------------------------------------------
-// Panel factorisation, blocked inside the panel (default).  The column step of the kernel above is bound by the
-// instructions a warp issues between two barriers (ncu: ~500 cycles of fixed latency + ~3.4 cycles per instruction
-// with 2 warps per scheduler; 400 instructions per column at 3 rows per thread, of which 82 DFMA on the 32-wide row
-// and 48 LDS of the pivot row).  Here the 32 columns are factored as four SUB-PANELS of 8 columns: inside a
+// Panel factorisation, register-resident and blocked inside the panel.  Local row r = t + NT i (i < R) lives in the
+// registers x[i][0..31] of thread t.  Per column j: (1) arg-max |x[.][j]| over rows >= j (ties -> smallest row, like the
+// scalar loop), two-stage reduction with ONE barrier; (2) the owner of the pivot row publishes it through shared
+// memory -- second barrier; (3) rank-1 update in registers.  Shared buffers are double-buffered by the parity of j.
+// An unblocked version (every column step updates all 32 columns of every row) was bound by the instructions a warp
+// issues between two barriers (ncu: ~500 cycles of fixed latency + ~3.4 cycles per instruction with 2 warps per
+// scheduler; 400 instructions per column at 3 rows per thread, of which 82 DFMA on the 32-wide row and 48 LDS of the
+// pivot row; 62 us per m = 768 panel against 45 us now).  Measured alternatives, not kept: one barrier per column (each
+// warp's local winner publishes its candidate row; equal), 384 threads x 2 rows for m > 512 (equal), rows loaded straight
+// into registers instead of through the staging tile (6 % slower).
+// Here the 32 columns are factored as four SUB-PANELS of 8 columns: inside a
 // sub-panel a column step touches only the 8 sub-panel columns of every row (<= 7 DFMA per row, 4 LDS, the pivot
 // row published as 8 doubles); the 24 (16, 8) columns to the right are updated once per sub-panel by a dense rank-8
 // update from registers -- no barrier, no pivot search in between:
@@ -443,122 +276,145 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
     // ---- LAPACK-style interchange of the `nleft` columns left of the panel (the L block of the first panel of
     // this outer block): gather every affected row, barrier, scatter
     if (nleft > 0) {
-        double v[8];
-        const int nel = naff * nleft; // <= 64 * 32
+        // one warp per (affected row, 32-column chunk): nleft <= 96 (fourth panel of a super-block), naff <= 64
+        constexpr int NQ = (64 * 3 + NT / 32 - 1) / (NT / 32);
+        double v[NQ];
+        const int w = nleft >> 5, nrc = naff * w;
 #pragma unroll
-        for (int q = 0; q < 8; q++) {
-            const int e = t + NT * q;
-            if (e < nel) { const int s = e / nleft, c = e - s * nleft; v[q] = A[(size_t)(k0 + s_pos[s_cur[s]]) * ld + k0 - nleft + c]; }
+        for (int q = 0; q < NQ; q++) {
+            const int rc = warp + (NT / 32) * q;
+            if ((NT / 32) * q >= nrc) break; // uniform
+            if (rc < nrc) {
+                const int s = w == 1 ? rc : (w == 2 ? rc >> 1 : (rc * 171) >> 9), ch = rc - s * w;
+                v[q] = A[(size_t)(k0 + s_pos[s_cur[s]]) * ld + k0 - nleft + 32 * ch + lane];
+            }
         }
         __syncthreads();
 #pragma unroll
-        for (int q = 0; q < 8; q++) {
-            const int e = t + NT * q;
-            if (e < nel) { const int s = e / nleft, c = e - s * nleft; if (s_cur[s] != s) A[(size_t)(k0 + s_pos[s]) * ld + k0 - nleft + c] = v[q]; }
+        for (int q = 0; q < NQ; q++) {
+            const int rc = warp + (NT / 32) * q;
+            if ((NT / 32) * q >= nrc) break; // uniform
+            if (rc < nrc) {
+                const int s = w == 1 ? rc : (w == 2 ? rc >> 1 : (rc * 171) >> 9), ch = rc - s * w;
+                if (s_cur[s] != s) A[(size_t)(k0 + s_pos[s]) * ld + k0 - nleft + 32 * ch + lane] = v[q];
+            }
         }
     }
 }
-#endif // PNL_V1
 
 // ------------------------------------------------------------------------------------------------------------
-// Row permutation + triangular solve for the columns right of a panel.  One thread per column, 128 columns per
-// CTA.  The panel kernel left the COMPOSED permutation of its 32 interchanges: naff affected local rows
-// pos[0..naff) (pos[s] = s for s < 32, then the pivot rows taken from below) and cur[s] = slot of the original
-// row that ends at pos[s].  Rows displaced to below the block always come from the top 32.
-//   mode 1: x = rows k0..k0+31 (after the permutation);                       x <- L11^-1 x
-//   mode 2: same, but first  x -= Lleft * u,  Lleft = A[k0..k0+31][k0-32..k0-1] (L21 of the first panel of the
-//           outer block, already permuted by k_panel), u = U1 rows k0-32..k0-1 of the column
+// Row permutation + (deferred left update) + triangular solve for the columns right of a panel.  One thread per
+// column, 128 columns per CTA.  The panel kernel left the COMPOSED permutation of its 32 interchanges: naff affected
+// local rows pos[0..naff) (pos[s] = s for s < 32, then the pivot rows taken from below) and cur[s] = slot of the
+// original row that ends at pos[s].  Rows displaced to below the block always come from the top 32.
+//   x = rows k0..k0+31 of the column (after the permutation)
+//   x -= Lleft u      Lleft = A[k0..k0+31][k0-nl..k0-1] (the L entries of the pivot rows left of this panel inside the
+//                     current outer block, already permuted by k_panel), u = rows k0-nl..k0-1 of the column (final U);
+//                     nl = nleft_lo for the columns left of c_split, nleft_hi from c_split on (columns inside a
+//                     128-wide super-block have received part of these updates from a restricted trailing update)
+//   x <- L11^-1 x
+// The left update runs on the FP64 tensor cores: per warp a (32 x 32) x (32 x 32) product per 32 rows of u (staged
+// by the warp's own lanes for its own 32 columns: only warp-level synchronisation), 128 DMMA + 64 fragment loads
+// instead of 1024 DFMA + 544 shared-memory loads per thread (a scalar sweep is bound by the shared-memory pipe).
+// The product goes back through the warp's slice of s_u to the one-column-per-thread layout of the substitution.
 // ------------------------------------------------------------------------------------------------------------
 #define TRSM_THREADS 128
+#ifndef TRSM_LEFT_MINB
+#define TRSM_LEFT_MINB 3
+#endif
 #define TRSM_LDT 34 // even: rows of the transposed triangles stay 16-byte aligned for double2 loads
 #define TRSM_LDU (TRSM_THREADS + 4) // row stride of s_u: = 4 (mod 16) doubles -> conflict-free DMMA fragment loads
-__global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, int c0, int mode, int a0, int a1)
+static size_t trsm_smem_bytes(int nleft) { return nleft > 0 ? (size_t)(32 * TRSM_LDU + nleft * TRSM_LDT) * sizeof(double) : 0; }
+
+template <bool LEFT> // LEFT = false: no pending left update anywhere (first panel of a block): 128 registers, 4 CTAs/SM
+__global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trsm(DevModel d, int k0, int c0, int nleft_lo, int nleft_hi, int c_split, int a0, int a1)
 {
     const int a = a0 + blockIdx.y;
     if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
     const int Np = d.Np, ld = d.ld;
     __shared__ __align__(16) double Lt[32 * TRSM_LDT];  // Lt[q][r] = L[r][q] of the panel's unit-lower 32x32 block
-    __shared__ __align__(16) double Llt[32 * TRSM_LDT]; // mode 2: Llt[q][r] = A[k0+r][k0-32+q]
     __shared__ int s_pos[64], s_cur[64];
-    extern __shared__ __align__(16) double s_u[]; // mode 2: [32][TRSM_LDU] rows k0-32..k0-1 (U1) of this column tile
+    extern __shared__ __align__(16) double s_dyn[];
+    double* s_u = s_dyn;                  // [32][TRSM_LDU] 32 rows of u for this column tile, then the product
+    double* Llt = s_dyn + 32 * TRSM_LDU;  // [nleft_hi][TRSM_LDT]: Llt[q][r] = A[k0+r][k0-nleft_hi+q]
     double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
     const int* aff = d.lu_aff + ((size_t)lay * (Np / RT_NB) + k0 / RT_NB) * RT_AFF_STRIDE;
     const int naff = aff[0];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int r = warp; r < 32; r += TRSM_THREADS / 32) {
         Lt[lane * TRSM_LDT + r] = A[(size_t)(k0 + r) * ld + k0 + lane];
-        if (mode == 2) Llt[lane * TRSM_LDT + r] = A[(size_t)(k0 + r) * ld + k0 - 32 + lane];
+        if (LEFT) for (int q = lane; q < nleft_hi; q += 32) Llt[q * TRSM_LDT + r] = A[(size_t)(k0 + r) * ld + k0 - nleft_hi + q];
     }
     if (tid < 64) { s_pos[tid] = aff[4 + tid]; s_cur[tid] = aff[68 + tid]; }
     __syncthreads();
     const int c = c0 + blockIdx.x * TRSM_THREADS + tid;
-    if (c >= ld) return;
+    if (c >= ld) return; // c0 and ld are multiples of 32: whole warps leave
+    const int nl = !LEFT ? 0 : ((c - lane) < c_split ? nleft_lo : nleft_hi); // warp-uniform
+    const int fr = lane >> 2, fk = lane & 3;
+    if (LEFT && nl > 0) {
+        // the pivot rows are needed only after the left update: lane r pulls row r of the warp's 256-byte column slice
+        // towards the SM meanwhile
+        {
+            const double* q = A + (size_t)(k0 + s_pos[s_cur[lane]]) * ld + (c - lane);
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(q));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(q + 16));
+        }
+        // P = Lleft u accumulated over chunks of 32 rows of u; the next chunk's loads are in flight during the DMMAs
+        double acc[2][4][2][2];
+#pragma unroll
+        for (int h = 0; h < 2; h++)
+#pragma unroll
+            for (int ti = 0; ti < 4; ti++)
+#pragma unroll
+                for (int tj = 0; tj < 2; tj++) acc[h][ti][tj][0] = acc[h][ti][tj][1] = 0.;
+        double un[32];
+#pragma unroll
+        for (int q = 0; q < 32; q++) un[q] = A[(size_t)(k0 - nl + q) * ld + c];
+        double* Bw = s_u + fk * TRSM_LDU + warp * 32;
+        for (int ch = 0; ch < nl; ch += 32) {
+#pragma unroll
+            for (int q = 0; q < 32; q++) s_u[q * TRSM_LDU + tid] = un[q];
+            __syncwarp();
+            if (ch + 32 < nl) {
+#pragma unroll
+                for (int q = 0; q < 32; q++) un[q] = A[(size_t)(k0 - nl + ch + 32 + q) * ld + c];
+            }
+            const double* Aw = Llt + (nleft_hi - nl + ch + fk) * TRSM_LDT + fr;
+#pragma unroll
+            for (int k4 = 0; k4 < 8; k4++) {
+                double af[4], bf[4];
+#pragma unroll
+                for (int ti = 0; ti < 4; ti++) af[ti] = Aw[4 * k4 * TRSM_LDT + ti * 8];
+#pragma unroll
+                for (int tj = 0; tj < 4; tj++) bf[tj] = Bw[4 * k4 * TRSM_LDU + tj * 8 + fr];
+#pragma unroll
+                for (int ti = 0; ti < 4; ti++)
+#pragma unroll
+                    for (int tj = 0; tj < 4; tj++) dmma884(acc[tj >> 1][ti][tj & 1][0], acc[tj >> 1][ti][tj & 1][1], af[ti], bf[tj]);
+            }
+            __syncwarp(); // every lane has read its fragments: the next chunk (or the product) may overwrite the slice
+        }
+#pragma unroll
+        for (int h = 0; h < 2; h++)
+#pragma unroll
+            for (int ti = 0; ti < 4; ti++)
+#pragma unroll
+                for (int tj = 0; tj < 2; tj++)
+                    *reinterpret_cast<double2*>(s_u + (ti * 8 + fr) * TRSM_LDU + warp * 32 + h * 16 + tj * 8 + 2 * fk) = make_double2(acc[h][ti][tj][0], acc[h][ti][tj][1]);
+        __syncwarp();
+    }
     // rows k0..k0+31 after the permutation: gathered straight from global memory (the same row for every thread of
     // the CTA -> coalesced); all gathers precede the stores of this column, columns are independent
     double x[32];
 #pragma unroll
     for (int r = 0; r < 32; r++) x[r] = A[(size_t)(k0 + s_pos[s_cur[r]]) * ld + c];
-    if (mode == 2) {
-#pragma unroll
-        for (int q = 0; q < 32; q++) s_u[q * TRSM_LDU + tid] = A[(size_t)(k0 - 32 + q) * ld + c];
-    }
     // rows displaced below the block receive ORIGINAL top rows (still untouched in memory: they are rewritten last)
     for (int s = 32; s < naff; s++)
         if (s_cur[s] != s) A[(size_t)(k0 + s_pos[s]) * ld + c] = A[(size_t)(k0 + s_pos[s_cur[s]]) * ld + c];
-    if (mode == 2) {
-#ifdef TRSM_FMA_LEFT
-        // x -= Lleft * u: column sweep, 32 independent accumulators per step
-#pragma unroll
-        for (int q = 0; q < 32; q++) {
-            const double2* lq = reinterpret_cast<const double2*>(Llt + q * TRSM_LDT);
-            const double uq = s_u[q * TRSM_LDU + tid]; // written by this thread: no barrier needed
-#pragma unroll
-            for (int r2 = 0; r2 < 16; r2++) {
-                const double2 l = lq[r2];
-                x[2 * r2] -= l.x * uq;
-                x[2 * r2 + 1] -= l.y * uq;
-            }
-        }
-#else
-        // x -= Lleft * u on the FP64 tensor cores: per warp a (32 x 32) x (32 x 32) product P = Lleft * U1 of the warp's own
-        // 32 columns (staged by its own lanes: only warp-level synchronisation), 128 DMMA + 64 fragment loads instead of
-        // 1024 DFMA + 544 shared-memory loads per thread (the scalar sweep is bound by the shared-memory pipe).  P goes back
-        // through the warp's slice of s_u to the one-column-per-thread layout of the forward substitution.
-        __syncwarp();
-        const int fr = lane >> 2, fk = lane & 3;
-        const double* Aw = Llt + fk * TRSM_LDT + fr;
-        double* Bw = s_u + fk * TRSM_LDU + warp * 32;
-#pragma unroll
-        for (int h = 0; h < 2; h++) { // two halves of 16 columns: 16 accumulators beside the 32 entries of x
-            double acc[4][2][2];
-#pragma unroll
-            for (int ti = 0; ti < 4; ti++)
-#pragma unroll
-                for (int tj = 0; tj < 2; tj++) acc[ti][tj][0] = acc[ti][tj][1] = 0.;
-#pragma unroll
-            for (int k4 = 0; k4 < 8; k4++) {
-                double af[4], bf[2];
-#pragma unroll
-                for (int ti = 0; ti < 4; ti++) af[ti] = Aw[4 * k4 * TRSM_LDT + ti * 8];
-#pragma unroll
-                for (int tj = 0; tj < 2; tj++) bf[tj] = Bw[4 * k4 * TRSM_LDU + h * 16 + tj * 8 + fr];
-#pragma unroll
-                for (int ti = 0; ti < 4; ti++)
-#pragma unroll
-                    for (int tj = 0; tj < 2; tj++) dmma884(acc[ti][tj][0], acc[ti][tj][1], af[ti], bf[tj]);
-            }
-            __syncwarp(); // every lane has read its fragments of these 16 columns: P may overwrite them
-#pragma unroll
-            for (int ti = 0; ti < 4; ti++)
-#pragma unroll
-                for (int tj = 0; tj < 2; tj++)
-                    *reinterpret_cast<double2*>(s_u + (ti * 8 + fr) * TRSM_LDU + warp * 32 + h * 16 + tj * 8 + 2 * fk) = make_double2(acc[ti][tj][0], acc[ti][tj][1]);
-        }
-        __syncwarp();
+    if (LEFT && nl > 0) {
 #pragma unroll
         for (int r = 0; r < 32; r++) x[r] -= s_u[r * TRSM_LDU + tid];
-#endif
     }
     // forward substitution, right-looking: after x[q] is final, every x[r], r > q, is updated independently
 #pragma unroll
@@ -589,7 +445,10 @@ __global__ void __launch_bounds__(TRSM_THREADS, 4) k_trsm(DevModel d, int k0, in
 #define GM_COLS 64
 #define GM_LDB 68
 
-template <int K, int ROWS>
+// NST stages of K columns each (kk0, kk0 + K, ...): the accumulators stay in registers across the stages, so a 128-deep
+// update (K = 64, NST = 2) reads and writes C once -- half the C traffic per flop of two 64-deep updates -- while the
+// A / B tiles of one stage still fit three CTAs per SM.
+template <int K, int ROWS, int NST>
 __global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
     const int a = a0 + blockIdx.z;
@@ -598,26 +457,29 @@ __global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevMode
     const int Np = d.Np, ld = d.ld;
     constexpr int LDA = K + 4;
     extern __shared__ __align__(16) double sm[];
-    double* As = sm;                 // [128][LDA]
+    double* As = sm;                 // [ROWS][LDA]
     double* Bs = sm + ROWS * LDA; // [K][68]
     double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int r0 = i0 + blockIdx.y * ROWS, cc0 = c0 + blockIdx.x * GM_COLS;
-    // ---- stage A (rows r0.., K columns at kk0) and B (K rows at kk0, 64 columns at cc0): 16-byte cp.async
+    // ---- stage A (rows r0.., K columns at kk) and B (K rows at kk, 64 columns at cc0): 16-byte cp.async
     constexpr int ACH = K / 2; // 16-byte chunks per A row
-    for (int e = tid; e < ROWS * ACH; e += ROWS * 2) {
-        const int r = e / ACH, ch = e - r * ACH;
-        double* dst = As + r * LDA + 2 * ch;
-        if (r0 + r < Np) cp_async16(dst, A + (size_t)(r0 + r) * ld + kk0 + 2 * ch);
-        else { dst[0] = 0.; dst[1] = 0.; }
-    }
-    for (int e = tid; e < K * (GM_COLS / 2); e += ROWS * 2) {
-        const int q = e >> 5, ch = e & 31;
-        double* dst = Bs + q * GM_LDB + 2 * ch;
-        if (cc0 + 2 * ch < c1) cp_async16(dst, A + (size_t)(kk0 + q) * ld + cc0 + 2 * ch);
-        else { dst[0] = 0.; dst[1] = 0.; }
-    }
-    asm volatile("cp.async.commit_group;");
+    auto stage = [&](int kk) {
+        for (int e = tid; e < ROWS * ACH; e += ROWS * 2) {
+            const int r = e / ACH, ch = e - r * ACH;
+            double* dst = As + r * LDA + 2 * ch;
+            if (r0 + r < Np) cp_async16(dst, A + (size_t)(r0 + r) * ld + kk + 2 * ch);
+            else { dst[0] = 0.; dst[1] = 0.; }
+        }
+        for (int e = tid; e < K * (GM_COLS / 2); e += ROWS * 2) {
+            const int q = e >> 5, ch = e & 31;
+            double* dst = Bs + q * GM_LDB + 2 * ch;
+            if (cc0 + 2 * ch < c1) cp_async16(dst, A + (size_t)(kk + q) * ld + cc0 + 2 * ch);
+            else { dst[0] = 0.; dst[1] = 0.; }
+        }
+        asm volatile("cp.async.commit_group;");
+    };
+    stage(kk0);
     // ---- accumulators <- C
     const int wr = warp >> 1, wc = warp & 1;
     const int rw = r0 + wr * 32, cw = cc0 + wc * 32;
@@ -634,21 +496,28 @@ __global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevMode
             }
             else acc[ti][tj][0] = acc[ti][tj][1] = 0.;
         }
-    asm volatile("cp.async.wait_group 0;");
-    __syncthreads();
     const double* Aw = As + (wr * 32 + fr) * LDA + (lane & 3);
     const double* Bw = Bs + (lane & 3) * GM_LDB + wc * 32 + fr;
+#pragma unroll 1
+    for (int st = 0; st < NST; st++) {
+        if (st > 0) {
+            __syncthreads(); // every warp is done with the previous stage's tiles
+            stage(kk0 + st * K);
+        }
+        asm volatile("cp.async.wait_group 0;");
+        __syncthreads();
 #pragma unroll 4
-    for (int k4 = 0; k4 < K / 4; k4++) {
-        double af[4], bf[4];
+        for (int k4 = 0; k4 < K / 4; k4++) {
+            double af[4], bf[4];
 #pragma unroll
-        for (int ti = 0; ti < 4; ti++) af[ti] = -Aw[ti * 8 * LDA + k4 * 4];
+            for (int ti = 0; ti < 4; ti++) af[ti] = -Aw[ti * 8 * LDA + k4 * 4];
 #pragma unroll
-        for (int tj = 0; tj < 4; tj++) bf[tj] = Bw[k4 * 4 * GM_LDB + tj * 8];
+            for (int tj = 0; tj < 4; tj++) bf[tj] = Bw[k4 * 4 * GM_LDB + tj * 8];
 #pragma unroll
-        for (int ti = 0; ti < 4; ti++)
+            for (int ti = 0; ti < 4; ti++)
 #pragma unroll
-            for (int tj = 0; tj < 4; tj++) dmma884(acc[ti][tj][0], acc[ti][tj][1], af[ti], bf[tj]);
+                for (int tj = 0; tj < 4; tj++) dmma884(acc[ti][tj][0], acc[ti][tj][1], af[ti], bf[tj]);
+        }
     }
 #pragma unroll
     for (int ti = 0; ti < 4; ti++)
@@ -755,25 +624,38 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
 // 0: 128x64 tiles, 2 CTAs/SM; 1 (default): 64x64 tiles, 3 CTAs/SM -- 3 % faster at N = 768.  A persistent, cp.async
 // double-buffered variant with C prefetch was measured 25 % SLOWER (3.6 vs 2.9 ms per slab-iteration): at K = 64 the
 // update moves 224 KB per tile through L2 for 4 us of DMMA work, i.e. ~8 TB/s chip-wide -- it is L2-bandwidth-bound,
-// not latency-bound, so deeper pipelining does not help; only a wider outer block (K = 128) would.
+// not latency-bound, so deeper pipelining does not help.  A second attempt -- K cut into stages of 32, cp.async double
+// buffering inside the CTA, still 3 CTAs/SM -- was also slower (2.54 vs 2.47 ms at K = 128, 3.14 vs 2.88 ms at K = 64).
 static int g_gemm_mode = 1;
 // Layer groups of one solve (development switch RT_B200_LU_GROUPS).  The layers of a batch are independent, so the
 // active list is cut into G slices whose factorisations run on G streams: while one slice sits in a latency-bound
 // panel (one register-file-filling CTA per SM, 200 layers = 1.35 waves on 148 SMs) the trailing updates of the other
 // slices fill the idle SMs.
 static int g_lu_groups = 2;
+// 128-wide super-blocks (third blocking level, RT_B200_LU_SUPER=1).  Measured at N = 768, 200 layers: the 128-deep
+// trailing update reads and writes C half as often and runs at 2.47 instead of 2.87 ms per slab-iteration, but 4 GFLOP of
+// the update move into the TRSM's left update (0.68 -> 0.95 ms) and the panel's wider interchange costs 0.04 ms: 5.42 vs
+// 5.52 ms per full-batch iteration, and SLOWER with few active layers (60 layers: 2.43 vs 2.35 ms), so the converged
+// CH3OH solve takes 210 instead of 207 ms.  Off by default; kept as a tested switch (tests/test_gpu_parity.py).
+static int g_lu_super = 0;
 #define LU_GROUP_MIN_LAYERS 48 // below this a slice no longer fills its share of the machine: fewer groups
 
+// K = 32: next panel's columns; 64: trailing update of a 64-wide block; 128: of a 128-wide super-block (two 64-deep stages)
 static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
     const int n = a1 - a0;
     const dim3 grid((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + GM_ROWS - 1) / GM_ROWS, n);
+    const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, n);
+    const size_t sm128 = (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), sm64 = (64 * 68 + 64 * GM_LDB) * sizeof(double);
     g_rt_launches++;
-    if (K == 32) k_gemm<32, 128><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
-    else if (g_gemm_mode == 0) k_gemm<64, 128><<<grid, 256, (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
+    if (K == 32) k_gemm<32, 128, 1><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
+    else if (K == 64) {
+        if (g_gemm_mode == 0) k_gemm<64, 128, 1><<<grid, 256, sm128, s>>>(d, i0, kk0, c0, c1, a0, a1);
+        else k_gemm<64, 64, 1><<<g64, 128, sm64, s>>>(d, i0, kk0, c0, c1, a0, a1);
+    }
     else {
-        const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, n);
-        k_gemm<64, 64><<<g64, 128, (64 * 68 + 64 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
+        if (g_gemm_mode == 0) k_gemm<64, 128, 2><<<grid, 256, sm128, s>>>(d, i0, kk0, c0, c1, a0, a1);
+        else k_gemm<64, 64, 2><<<g64, 128, sm64, s>>>(d, i0, kk0, c0, c1, a0, a1);
     }
 }
 
@@ -811,12 +693,16 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
         launch_panel(d, st[g], k0, nleft, ga0[g], ga1[g]);
         rt_prof_end(m, c_panel, st[g]);
     };
-    auto trsm = [&](int g, int k0, int mode) {
+    // columns [k0+32, ld) right of the panel at k0: left update nleft_lo wide left of c_split, nleft_hi wide from c_split on
+    auto trsm = [&](int g, int k0, int nleft_lo, int nleft_hi, int c_split) {
         const int c0 = k0 + 32;
-        const double nc = ld - c0;
-        rt_prof_begin(m, c_trsm, st[g], (mode == 2 ? 3. : 1.) * 32. * 32. * nc, (mode == 2 ? 24. : 16.) * 32. * nc);
+        const double nc = ld - c0, ncl = std::max(0, std::min(c_split, ld) - c0), nch = nc - ncl;
+        rt_prof_begin(m, c_trsm, st[g], 32. * 32. * nc + 2. * 32. * (nleft_lo * ncl + nleft_hi * nch),
+                      16. * 32. * nc + 8. * (nleft_lo * ncl + nleft_hi * nch));
         g_rt_launches++;
-        k_trsm<<<dim3((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]), TRSM_THREADS, mode == 2 ? 32 * TRSM_LDU * sizeof(double) : 0, st[g]>>>(d, k0, c0, mode, ga0[g], ga1[g]);
+        const dim3 grid((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]);
+        if (nleft_hi > 0) k_trsm<true><<<grid, TRSM_THREADS, trsm_smem_bytes(nleft_hi), st[g]>>>(d, k0, c0, nleft_lo, nleft_hi, c_split, ga0[g], ga1[g]);
+        else k_trsm<false><<<grid, TRSM_THREADS, 0, st[g]>>>(d, k0, c0, 0, 0, c_split, ga0[g], ga1[g]);
         rt_prof_end(m, c_trsm, st[g]);
     };
     auto gemm = [&](int g, int K, int i0, int kk0, int c0, int c1) {
@@ -825,22 +711,44 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
         launch_gemm(d, st[g], K, i0, kk0, c0, c1, ga0[g], ga1[g]);
         rt_prof_end(m, c_gemm, st[g]);
     };
-    // the groups' launches are issued interleaved, step by step, so that every stream always has work queued
-    for (int k0 = 0; k0 < Np; k0 += 64) {
+    auto set_layers = [&](int g) { m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1); };
+    // Three blocking levels: panels of 32 columns inside blocks of 64 inside SUPER-BLOCKS of 128 (g_lu_super; while at
+    // least 128 columns remain).  Inside a super-block at k0 the update of the columns right of it is deferred: the
+    // four panels' TRSMs subtract the pending part L_left U themselves (32 rows each), the block-level update touches
+    // only the super-block's own columns, and ONE 128-deep trailing update follows -- C is read and written once per
+    // 128 eliminated columns instead of once per 64.  The groups' launches are issued interleaved, step by step, so
+    // that every stream always has work queued.
+    for (int k0 = 0; k0 < Np;) {
+        const bool super = g_lu_super && Np - k0 >= 128;
+        const int cend = super ? k0 + 128 : ld; // columns the block-level (64-deep) update covers
         for (int g = 0; g < G; g++) {
-            m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1);
+            set_layers(g);
             panel(g, k0, 0);
-            trsm(g, k0, 1);
+            trsm(g, k0, 0, 0, ld);
             if (k0 + 32 < Np) gemm(g, 32, k0 + 32, k0, k0 + 32, k0 + 64);
         }
         if (k0 + 32 < Np) {
             for (int g = 0; g < G; g++) {
-                m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1);
+                set_layers(g);
                 panel(g, k0 + 32, 32);
-                trsm(g, k0 + 32, 2);
-                if (k0 + 64 < Np) gemm(g, 64, k0 + 64, k0, k0 + 64, ld);
+                trsm(g, k0 + 32, 32, 32, ld);
+                if (k0 + 64 < Np) gemm(g, 64, k0 + 64, k0, k0 + 64, cend);
             }
         }
+        if (!super) { k0 += 64; continue; }
+        for (int g = 0; g < G; g++) {
+            set_layers(g);
+            panel(g, k0 + 64, 64);
+            trsm(g, k0 + 64, 0, 64, k0 + 128); // the super-block's own columns have the first block's update already
+            gemm(g, 32, k0 + 96, k0 + 64, k0 + 96, k0 + 128);
+        }
+        for (int g = 0; g < G; g++) {
+            set_layers(g);
+            panel(g, k0 + 96, 96);
+            trsm(g, k0 + 96, 96, 96, ld);
+            if (k0 + 128 < Np) gemm(g, 128, k0 + 128, k0, k0 + 128, ld);
+        }
+        k0 += 128;
     }
     for (int g = 0; g < G; g++) {
         m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1);
@@ -860,19 +768,19 @@ int lu_max_np() { return PNL_MAXROWS; }
 
 cudaError_t lu_kernels_init()
 {
-    cudaError_t e = cudaFuncSetAttribute(k_panel<1, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 33 * (int)sizeof(double));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_panel<2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 512 * 33 * (int)sizeof(double));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_panel<PNL_BIG_R, PNL_BIG_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 768 * 33 * (int)sizeof(double));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_gemm<64, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_trsm, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * TRSM_LDU * (int)sizeof(double));
-    if (e != cudaSuccess) return e;
-    if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switch
+    if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switches
     if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
-    e = cudaFuncSetAttribute(k_gemm<64, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (64 * 68 + 64 * GM_LDB) * (int)sizeof(double));
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_gemm<32, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (GM_ROWS * 36 + 32 * GM_LDB) * (int)sizeof(double));
+    if (const char* gs = getenv("RT_B200_LU_SUPER")) g_lu_super = atoi(gs);
+    const int sm128 = (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double), sm64 = (64 * 68 + 64 * GM_LDB) * (int)sizeof(double);
+    const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    cudaError_t e = cudaFuncSetAttribute(k_panel<1, 256>, at, 256 * 33 * (int)sizeof(double));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<2, 256>, at, 512 * 33 * (int)sizeof(double));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<PNL_BIG_R, PNL_BIG_NT>, at, 768 * 33 * (int)sizeof(double));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm<true>, at, (int)trsm_smem_bytes(96));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 128, 1>, at, sm128);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 128, 2>, at, sm128);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 64, 1>, at, sm64);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 64, 2>, at, sm64);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 128, 1>, at, (GM_ROWS * 36 + 32 * GM_LDB) * (int)sizeof(double));
+    return e;
 }

@@ -142,6 +142,7 @@ def test_retry_policy_non_methanol(solver_mod, best_checker, problems):
     m = solver_mod.Model(p)
     pop1, st1 = m.calculate_populations()                     # first (accelerated) attempt alone
     pop, st = m.calc_molecular_populations(acceleration=True)  # with the retry policy
+    pop_next, _ = m.calc_new_pop(pop)                           # one more plain step from the returned populations
     m.close()
     pop_o1, st_o1, _ = best_checker.solve(p, nthreads=8)
     pop_o, st_o, _ = best_checker.solve(p, retry=True, nthreads=8)
@@ -156,10 +157,14 @@ def test_retry_policy_non_methanol(solver_mod, best_checker, problems):
     # retried layers really were re-run un-accelerated from a fresh start: more iterations than the accelerated cap
     retried = st1["converged"] == 0
     assert np.all(st["iters"][retried] > p.max_iter)
-    # a layer the accelerated attempt decides differently (chaotic, see test_live_solve_vs_oracle) still ends at the
-    # same fixed point, to the accuracy of the 1e-5 stopping rule, on the levels that carry population
+    # A layer the accelerated attempt decides differently (chaotic, see test_live_solve_vs_oracle) stops on another path
+    # (accelerated on one side, un-accelerated retry on the other).  Both stop when one step changes the populations by
+    # less than 1e-5, which for the slowly contracting un-accelerated map is up to ~1e-5 / (1 - rho) away from the fixed
+    # point.  Checked at the fixed-point level: one more plain step leaves the returned populations unchanged to the
+    # order of the stopping rule, and the two answers agree to the accuracy that rule can give.
     diff = ~same & (st["converged"] == 1) & (st_o["converged"] == 1)
-    assert rel_err(pop[diff], pop_o[diff], 1e-12) < 1e-3
+    assert rel_err(pop_next[diff], pop[diff], 1e-12) < 1e-4
+    assert rel_err(pop[diff], pop_o[diff], 1e-12) < 2e-2
 
 
 def test_given_start_and_iteration_cap(solver_mod, best_checker, problems):
@@ -281,3 +286,33 @@ def test_full_size_oh_overlap_properties(solver_mod, best_checker):
         if st_o["converged"][0]:
             assert abs(int(st_o["iters"][0]) - int(st["iters"][l])) <= 1
             assert rel_err(pop[l], pop_o[0], 1e-30) < 1e-6
+
+
+@pytest.mark.gpu
+def test_super_block_lu_switch(problems):
+    """RT_B200_LU_SUPER=1 (128-wide super-blocks, third blocking level of the LU; off by default, lu_kernels.cu): the
+    switch is read once per process, so the check runs in a child process -- one calc_new_pop of a CH3OH-like slab
+    (N = 240, Np = 256: two super-blocks) and of an H2O-like slab (Np with a 32-column remainder) must agree with the default
+    blocking to rounding."""
+    import os, subprocess, sys, json
+    code = (
+        "import sys, json, numpy as np; sys.path.insert(0, %r)\n"
+        "from radiative_transfer_b200 import solver, synthetic\n"
+        "out = {}\n"
+        "for name, p in (('ch3oh', synthetic.small('ch3oh_mid', 5)), ('h2o', synthetic.config_h2o(L=4, N=290))):\n"
+        "    m = solver.Model(p); b = m.boundary_layer_populations(); new, eq = m.calc_new_pop(b); m.close()\n"
+        "    out[name] = [p.N, new.tolist()]\n"
+        "print(json.dumps(out))\n" % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    res = {}
+    for sw in ("0", "1"):
+        env = dict(os.environ, RT_B200_LU_SUPER=sw)
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        res[sw] = json.loads(r.stdout.strip().splitlines()[-1])
+    for name in res["0"]:
+        n0, a = res["0"][name]
+        n1, b = res["1"][name]
+        a, b = np.asarray(a), np.asarray(b)
+        assert n0 == n1 and a.shape == b.shape
+        assert np.allclose(a.sum(axis=1), 1.0, atol=1e-9) and np.allclose(b.sum(axis=1), 1.0, atol=1e-9)
+        assert rel_err(a, b, 1e-30) < 1e-8, name
