@@ -260,6 +260,14 @@ rt_status rt_maser_postpass(rt_model* m, const double* pop, int nb_trans, const 
                             double* inv_arr, double* gain_arr, double* scalars /*[nb_trans][5]*/,
                             double* tau_vs_aspect, double* tau_vs_freq);
 
+/* The oH2O 6_16 -> 5_23 (22.2 GHz) special case of calc_gain (transition_data.cpp:249-260): the gain of that one line
+ * uses vel = sqrt((sqrt(2kT/m) + thermal_offset)^2 + v_turb^2), thermal_offset = 5e4 cm/s in the reference (hyperfine
+ * splitting).  The reference recognises the line by the quantum numbers (v, j, k1, k2) of its levels, which the flat
+ * model does not carry: the caller (who holds the energy_diagram) names it by level indices once per model.
+ * up < 0 clears it.  Affects rt_maser_postpass only (gain, tau_eff, lay_nb_hg; not the line profile, as in the
+ * reference).  ABI 3. */
+rt_status rt_set_gain_width_line(rt_model* m, int up, int low, double thermal_offset);
+
 /* Limiting maser luminosity and pump/loss rates: lim_luminosity_lvg (maser_luminosity.cpp:7-106),
  * calc_exc_temp (transition_data.cpp:225-237) and calc_saturation_depth (transition_data.cpp:456-483) for each listed
  * transition (up[i] > low[i]).  pop HOST [L*N].  Per transition and layer, all [nb_trans][L], any may be NULL:

@@ -180,6 +180,25 @@ inline void flatten_model(const iteration_scheme_lvg* scheme, const energy_diagr
     d.dust_ncomp = dm->nb_of_comp; d.dust = f.dust.data();
 }
 
+// The oH2O 6_16 -> 5_23 (22.2 GHz) line whose gain transition_data_container::calc_gain evaluates with a widened
+// thermal width (transition_data.cpp:249-260): found by the quantum numbers the reference tests for and handed to the
+// library by level index (rt_set_gain_width_line), once per model.  Returns false (and clears the setting) for any
+// other molecule.
+inline bool set_h2o_22ghz_line(rt_model* m, const energy_diagram* levels)
+{
+    int up = -1, low = -1;
+    if (levels->mol.name == "oH2O" && levels->mol.isotop == 1) {
+        for (int i = 0; i < levels->nb_lev; i++) {
+            const energy_level& lv = levels->lev_array[i];
+            if (lv.v == 0 && lv.j == 6 && lv.k1 == 1 && lv.k2 == 6) up = i;
+            if (lv.j == 5 && lv.k1 == 2 && lv.k2 == 3 && low < 0) low = i;
+        }
+    }
+    const bool found = up >= 0 && low >= 0 && low < up;
+    rt_set_gain_width_line(m, found ? up : -1, low, 5.e+4);
+    return found;
+}
+
 struct flat_cloud {
     std::vector<double> a[12], dust_conc;
     rt_layer_soa soa;

@@ -150,9 +150,26 @@ class Checker:
         assert rc == 0, rc
         return pop, st, sec.value
 
-    def maser_postpass(self, p, pop, up, low, nb_freq=300, nb_aspect=37, delta_aspect=0.25, velocity_shift=5.e5):
+    def maser_postpass(self, p, pop, up, low, nb_freq=300, nb_aspect=37, delta_aspect=0.25, velocity_shift=5.e5,
+                       gain_width_line=None):
         """transition_data_container::calc_inv / calc_gain / calc_line_profile.  The reference fixes
-        nb_freq=300, nb_aspect=37, delta_aspect=0.25, velocity_shift=5e5 (transition_data.cpp:16-18,191)."""
+        nb_freq=300, nb_aspect=37, delta_aspect=0.25, velocity_shift=5e5 (transition_data.cpp:16-18,191).
+        gain_width_line = (up, low): that line gets the oH2O 22 GHz special width of calc_gain (:249-260; the molecule
+        must be named "oH2O" for the compiled reference to take that branch)."""
+        gw = (-1, -1) if gain_width_line is None else (int(gain_width_line[0]), int(gain_width_line[1]))
+        if self.kind == "ref":
+            self.lib.ref_set_gain_width_line(gw[0], gw[1])
+        else:
+            self.lib.ora_set_gain_width_line(gw[0], gw[1], C.c_double(5.e4))
+        try:
+            return self._maser_postpass(p, pop, up, low, nb_freq, nb_aspect, delta_aspect, velocity_shift)
+        finally:
+            if self.kind == "ref":
+                self.lib.ref_set_gain_width_line(-1, -1)
+            else:
+                self.lib.ora_set_gain_width_line(-1, -1, C.c_double(0.))
+
+    def _maser_postpass(self, p, pop, up, low, nb_freq, nb_aspect, delta_aspect, velocity_shift):
         d, s, hold = self._views(p)
         pop = np.ascontiguousarray(pop, dtype=np.float64)
         up = np.ascontiguousarray(up, dtype=np.int32); low = np.ascontiguousarray(low, dtype=np.int32)

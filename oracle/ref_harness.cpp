@@ -53,6 +53,12 @@ void calc_molecular_populations(cloud_data* cloud, iteration_scheme_lvg* it_sche
                                 einstein_coeff* mol_einst, collisional_transitions* mol_coll, double* mol_popul,
                                 int nb_lev, bool acceleration, int verbosity);
 
+// The flat model carries no k1 / k2 quantum numbers.  To exercise the oH2O 6_16 -> 5_23 special line width of
+// calc_gain (transition_data.cpp:249-260) the caller names one line by level indices; those two levels then get the
+// quantum numbers the reference tests for (v = 0, j/k1/k2 = 6/1/6 and 5/2/3).  up < 0: none.
+static int g_gw_up = -1, g_gw_low = -1;
+extern "C" void ref_set_gain_width_line(int up, int low) { g_gw_up = up; g_gw_low = low; }
+
 namespace {
 
 // ---------------------------------------------------------------------------------------------------------
@@ -69,6 +75,8 @@ struct synth_diagram : public energy_diagram {
             lev.v = d->v ? d->v[i] : 0;
             lev.j = d->j ? d->j[i] : 0.;
             lev.energy = d->energy[i];
+            if (i == g_gw_up) { lev.v = 0; lev.j = 6; lev.k1 = 1; lev.k2 = 6; }
+            if (i == g_gw_low) { lev.v = 0; lev.j = 5; lev.k1 = 2; lev.k2 = 3; }
             lev_array.push_back(lev);
         }
         nb_lev = d->nb_lev;

@@ -981,9 +981,16 @@ int ora_solve(const rt_model_desc* d, const rt_layer_soa* lay, double* pop, int 
     return 0;
 }
 
-/* transition_data_container::calc_inv (transition_data.cpp:210-223), calc_gain (:240-294, general line-width
- * branch: the oH2O 6_16-5_23 special width needs the k1/k2 quantum numbers, which the flat model does not carry)
- * and calc_line_profile (:296-378) for listed transitions.  scalars [nb_trans][5] = {inv, gain, tau_eff, tau_max,
+/* The line whose gain uses the widened thermal width of the oH2O 6_16 -> 5_23 (22.2 GHz) special case of calc_gain
+ * (transition_data.cpp:249-260): vel = sqrt((sqrt(2kT/m) + offset)^2 + v_turb^2), offset = 5e4 cm/s in the reference.
+ * The reference recognises the line by its quantum numbers (j, k1, k2), which the flat model does not carry, so the
+ * caller names it by level indices.  up < 0: no such line. */
+static int g_gw_up = -1, g_gw_low = -1;
+static double g_gw_offset = 0.;
+void ora_set_gain_width_line(int up, int low, double thermal_offset) { g_gw_up = up; g_gw_low = low; g_gw_offset = thermal_offset; }
+
+/* transition_data_container::calc_inv (transition_data.cpp:210-223), calc_gain (:240-294, incl. the special line
+ * width above) and calc_line_profile (:296-378) for listed transitions.  scalars [nb_trans][5] = {inv, gain, tau_eff, tau_max,
  * lay_nb_hg}.  nb_freq / nb_aspect / delta_aspect / velocity_shift: 300 / 37 / 0.25 / 5e5 in the reference
  * (transition_data.cpp:16-18,191). */
 int ora_maser_postpass(const rt_model_desc* d, const rt_layer_soa* lay, const double* pop, int nb_trans, const int* up,
@@ -1013,7 +1020,12 @@ int ora_maser_postpass(const rt_model_desc* d, const rt_layer_soa* lay, const do
         }
         inv /= lay->height;
         for (int k = 0; k < L; k++) { /* calc_gain :248-272 */
-            const double vel = pow(2. * pr->boltzmann_constant * lay->temp_n[k] / d->mol_mass + lay->vel_turb[k] * lay->vel_turb[k], 0.5);
+            double vel;
+            if (u == g_gw_up && l == g_gw_low) /* :257-260 */
+                vel = sqrt(pow(sqrt(2. * pr->boltzmann_constant * lay->temp_n[k] / d->mol_mass) + g_gw_offset, 2.)
+                           + lay->vel_turb[k] * lay->vel_turb[k]);
+            else
+                vel = pow(2. * pr->boltzmann_constant * lay->temp_n[k] / d->mol_mass + lay->vel_turb[k] * lay->vel_turb[k], 0.5);
             const double line_gain = inv_l[k] * gu * A * pr->onedivby_sqrt_pi * lay->mol_conc[k] / (energy_th * pr->eight_pi * vel);
             const double d_abs = dust_absorption(m, energy, lay->dust_conc + (size_t)k * lay->dust_ncomp);
             gain_l[k] = line_gain - d_abs;

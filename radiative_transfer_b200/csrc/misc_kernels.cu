@@ -31,16 +31,16 @@ void launch_intensity_single(const DevModel& d, cudaStream_t s, int lay, int up,
 
 // ------------------------------------------------------------------------------------------------------------
 // K5: post-solve maser quantities of listed transitions, transition_data.cpp:210-378
-// (calc_inv :210-223, calc_gain :240-294 without the oH2O 22 GHz special width, calc_line_profile :296-378).
+// (calc_inv :210-223, calc_gain :240-294 incl. the oH2O 22 GHz special width :249-260, calc_line_profile :296-378).
 // One CTA per transition.  Layer sums run in ascending layer order like the reference's loops.
 // ------------------------------------------------------------------------------------------------------------
 struct PostArgs {
     const double* pop;  // [L][N]
     const int *up, *low;
     const double* sigma; // [T][ncomp] dust cross-section at the transition energy
-    const double *dz, *vel_n, *vgrid; // [L], [L], [nb_freq]
-    double height, delta_aspect;
-    int nb_freq, nb_aspect;
+    const double *dz, *vel_n, *vgrid, *vel_turb; // [L], [L], [nb_freq], [L]
+    double height, delta_aspect, gw_offset;
+    int nb_freq, nb_aspect, gw_up, gw_low; // rt_set_gain_width_line: the line with the widened thermal width in calc_gain
     double *inv_arr, *gain_arr, *scalars, *tau_aspect, *tau_freq;
 };
 
@@ -59,7 +59,12 @@ __global__ void __launch_bounds__(320) k_postpass(DevModel d, PostArgs a)
         const double up_pop = a.pop[(size_t)lay * N + u], low_pop = a.pop[(size_t)lay * N + l];
         const double inv = up_pop / gu - low_pop / gl; // :218
         const double vel = d.vel_width[lay];           // pow(2kT/m + vt^2, 0.5), :261-262 == iteration_lvg.cpp:65
-        const double line_gain = inv * gu * Aul * d.prm.onedivby_sqrt_pi * d.mol_conc[lay] / (energy_th * d.prm.eight_pi * vel); // :266-268
+        double vel_gain = vel;
+        if (u == a.gw_up && l == a.gw_low) {           // :257-260: thermal width + hyperfine offset, then the turbulent part
+            const double th = sqrt(2. * d.prm.boltzmann_constant * d.temp_n[lay] / d.mol_mass) + a.gw_offset;
+            vel_gain = sqrt(th * th + a.vel_turb[lay] * a.vel_turb[lay]);
+        }
+        const double line_gain = inv * gu * Aul * d.prm.onedivby_sqrt_pi * d.mol_conc[lay] / (energy_th * d.prm.eight_pi * vel_gain); // :266-268
         double d_abs = 0.;
         for (int c = 0; c < d.ncomp; c++) d_abs += a.sigma[(size_t)t * d.ncomp + c] * d.dust_conc[(size_t)lay * d.ncomp + c];
         s_inv[lay] = inv;

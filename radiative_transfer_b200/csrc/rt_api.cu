@@ -108,7 +108,7 @@ const char* rt_status_string(rt_status s)
 }
 
 const char* rt_last_error(const rt_model* m) { return m ? m->last_error.c_str() : g_create_error.c_str(); }
-int rt_abi_version(void) { return 2; }
+int rt_abi_version(void) { return 3; }
 
 } // extern "C"
 
@@ -889,9 +889,9 @@ struct PostArgs {
     const double* pop;
     const int *up, *low;
     const double* sigma;
-    const double *dz, *vel_n, *vgrid;
-    double height, delta_aspect;
-    int nb_freq, nb_aspect;
+    const double *dz, *vel_n, *vgrid, *vel_turb;
+    double height, delta_aspect, gw_offset;
+    int nb_freq, nb_aspect, gw_up, gw_low;
     double *inv_arr, *gain_arr, *scalars, *tau_aspect, *tau_freq;
 };
 void launch_postpass_impl(const DevModel& d, cudaStream_t s, const PostArgs& a, int nb_trans);
@@ -945,6 +945,15 @@ extern "C" rt_status rt_intensity(rt_model* m, int lay, int up, int low, const d
     return RT_OK;
 }
 
+extern "C" rt_status rt_set_gain_width_line(rt_model* m, int up, int low, double thermal_offset)
+{
+    if (!m) return RT_ERR_INVALID;
+    if (up < 0) { m->gw_up = m->gw_low = -1; m->gw_offset = 0.; return RT_OK; }
+    if (up >= m->d.N || low < 0 || low >= up) return RT_ERR_INVALID;
+    m->gw_up = up; m->gw_low = low; m->gw_offset = thermal_offset;
+    return RT_OK;
+}
+
 extern "C" rt_status rt_maser_postpass(rt_model* m, const double* pop, int nb_trans, const int* up, const int* low,
                                        int nb_freq, int nb_aspect, double delta_aspect, double velocity_shift,
                                        double* inv_arr, double* gain_arr, double* scalars, double* tau_vs_aspect,
@@ -979,6 +988,8 @@ extern "C" rt_status rt_maser_postpass(rt_model* m, const double* pop, int nb_tr
     a.dz = (const double*)up_d(m->h_dz.data(), sizeof(double) * L);
     a.vel_n = (const double*)up_d(m->h_vel_n.data(), sizeof(double) * L);
     a.vgrid = (const double*)up_d(vgrid.data(), sizeof(double) * nb_freq);
+    a.vel_turb = (const double*)up_d(m->h_vel_turb.data(), sizeof(double) * L);
+    a.gw_up = m->gw_up; a.gw_low = m->gw_low; a.gw_offset = m->gw_offset;
     a.height = m->h_height; a.delta_aspect = delta_aspect; a.nb_freq = nb_freq; a.nb_aspect = nb_aspect;
     a.inv_arr = (double*)out_d(sizeof(double) * (size_t)nb_trans * L);
     a.gain_arr = (double*)out_d(sizeof(double) * (size_t)nb_trans * L);

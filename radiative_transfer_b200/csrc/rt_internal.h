@@ -97,6 +97,8 @@ struct rt_model {
     std::vector<double> h_h2_conc, h_mol_conc, h_velg; // rt_lim_luminosity: ph2 + oh2, mol_conc, dv/dz per layer
     std::vector<int> h_g;
     double h_height = 0.;
+    int gw_up = -1, gw_low = -1;   // rt_set_gain_width_line
+    double gw_offset = 0.;
     long long iters_enqueued = 0;
     std::vector<std::vector<double>> h_dust_en, h_dust_abs;
     std::vector<double> h_dust_exp;

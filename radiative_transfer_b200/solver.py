@@ -18,7 +18,7 @@ from . import abi
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_B200_LIB", os.path.join(HERE, "librt_b200.so"))  # override: kernel-variant experiments only
 _lib = None
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 ENTRY_POINTS = [
     "rt_params_default", "rt_status_string", "rt_last_error", "rt_abi_version", "rt_model_create", "rt_model_destroy",
@@ -26,7 +26,7 @@ ENTRY_POINTS = [
     "rt_calc_molecular_populations", "rt_solve_device", "rt_get_status", "rt_get_populations", "rt_set_populations",
     "rt_profile_reset", "rt_profile_get", "rt_iterations_enqueued", "rt_maser_postpass", "rt_cloud_rebuild",
     "rt_profile_get_work", "rt_launch_count", "rt_timer_begin", "rt_timer_end", "rt_device_fp64_peak",
-    "rt_lim_luminosity",
+    "rt_lim_luminosity", "rt_set_gain_width_line",
 ]
 
 
@@ -174,6 +174,10 @@ class Model:
         self._ck(self.L_.rt_set_populations(self.h, abi.dptr(pop)), "rt_set_populations")
 
     # -- transition_data_container::calc_inv / calc_gain / calc_line_profile ------------------------------------
+    def set_gain_width_line(self, up: int, low: int, thermal_offset: float = 5.e4):
+        """The oH2O 6_16 -> 5_23 special line width of calc_gain (transition_data.cpp:249-260); up < 0 clears it."""
+        self._ck(lib().rt_set_gain_width_line(self.h, int(up), int(low), C.c_double(thermal_offset)), "rt_set_gain_width_line")
+
     def maser_postpass(self, pop, up, low, nb_freq=300, nb_aspect=37, delta_aspect=0.25, velocity_shift=5.e5):
         pop = np.ascontiguousarray(pop, dtype=np.float64)
         up = np.ascontiguousarray(up, dtype=np.int32); low = np.ascontiguousarray(low, dtype=np.int32)

@@ -316,3 +316,27 @@ def test_super_block_lu_switch(problems):
         assert n0 == n1 and a.shape == b.shape
         assert np.allclose(a.sum(axis=1), 1.0, atol=1e-9) and np.allclose(b.sum(axis=1), 1.0, atol=1e-9)
         assert rel_err(a, b, 1e-30) < 1e-8, name
+
+
+@pytest.mark.gpu
+def test_h2o_22ghz_gain_width(solver_mod, best_checker, problems):
+    """rt_set_gain_width_line: the oH2O 6_16 -> 5_23 special line width of calc_gain (transition_data.cpp:249-260)."""
+    p = problems("h2o_small", 4)
+    m = solver_mod.Model(p)
+    b = m.boundary_layer_populations()
+    up, low = G.maser_lines(p, b)
+    line = (int(up[0]), int(low[0]))
+    plain = m.maser_postpass(b, up, low)
+    m.set_gain_width_line(*line)
+    got = m.maser_postpass(b, up, low)
+    m.set_gain_width_line(-1, -1)
+    cleared = m.maser_postpass(b, up, low)
+    with pytest.raises(solver_mod.RtError):
+        m.set_gain_width_line(3, 7)  # up must be the upper level
+    m.close()
+    want = best_checker.maser_postpass(p, b, up, low, gain_width_line=line)
+    assert not np.allclose(got["gain"][0], plain["gain"][0], rtol=1e-3, atol=0)
+    for k in ("inv", "gain", "scalars", "tau_vs_aspect", "tau_vs_freq"):
+        scale = np.max(np.abs(want[k])) + 1e-300
+        assert np.max(np.abs(got[k] - want[k])) / scale < 1e-10, k
+        assert np.array_equal(cleared[k], plain[k]), k

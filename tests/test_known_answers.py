@@ -61,3 +61,27 @@ def test_esc_func_reproduces_nodes_and_clamps(port, problems):
     lo = port.esc_func(p, np.array([p.lvg_gamma[0] / 10]), np.array([p.lvg_delta[0] / 10]))
     hi = port.esc_func(p, np.array([p.lvg_gamma[-1] * 10]), np.array([p.lvg_delta[-1] * 10]))
     assert lo[0] == p.lvg_p[0, 0] and hi[0] == p.lvg_p[-1, -1]
+
+
+def test_h2o_22ghz_gain_width(port, ref, problems):
+    """calc_gain's oH2O 6_16 -> 5_23 special line width (transition_data.cpp:249-260): the compiled reference takes that
+    branch when the two levels carry the quantum numbers it tests for (the harness sets them on the named line); the
+    restatement names the line by level indices.  Only the gain side changes (gain, tau_eff), not the line profile."""
+    import golden_cases as G
+    p = problems("h2o_small", 4)
+    assert p.mol_name == "oH2O"
+    b = port.boundary(p)
+    up, low = G.maser_lines(p, b)
+    line = (int(up[0]), int(low[0]))
+    plain = ref.maser_postpass(p, b, up, low)
+    special = ref.maser_postpass(p, b, up, low, gain_width_line=line)
+    mine = port.maser_postpass(p, b, up, low, gain_width_line=line)
+    assert not np.allclose(special["gain"][0], plain["gain"][0], rtol=1e-3, atol=0)   # the branch was really taken
+    assert np.array_equal(special["gain"][1:], plain["gain"][1:])                      # other lines untouched
+    assert np.array_equal(special["tau_vs_freq"], plain["tau_vs_freq"])                # calc_line_profile unaffected
+    for k in ("inv", "gain", "scalars", "tau_vs_aspect", "tau_vs_freq"):
+        scale = np.max(np.abs(special[k])) + 1e-300
+        assert np.max(np.abs(mine[k] - special[k])) / scale < 1e-12, k
+    # and the setting does not leak into the next call
+    again = port.maser_postpass(p, b, up, low)
+    assert np.max(np.abs(again["gain"] - plain["gain"])) / (np.max(np.abs(plain["gain"])) + 1e-300) < 1e-12
