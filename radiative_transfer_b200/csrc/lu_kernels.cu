@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int 
 static size_t trsm_smem_bytes(int nleft) { return nleft > 0 ? (size_t)(32 * TRSM_LDU + nleft * TRSM_LDT) * sizeof(double) : 0; }
 
 template <bool LEFT> // LEFT = false: no pending left update anywhere (first panel of a block): 128 registers, 4 CTAs/SM
-__global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trsm(DevModel d, int k0, int c0, int nleft_lo, int nleft_hi, int c_split, int a0, int a1)
+__global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trsm(DevModel d, int k0, int c0, int c_end, int nleft_lo, int nleft_hi, int c_split, int a0, int a1)
 {
     const int a = a0 + blockIdx.y;
     if (a >= a1 || a >= *d.n_active) return;
@@ -349,7 +349,7 @@ __global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trs
     if (tid < 64) { s_pos[tid] = aff[4 + tid]; s_cur[tid] = aff[68 + tid]; }
     __syncthreads();
     const int c = c0 + blockIdx.x * TRSM_THREADS + tid;
-    if (c >= ld) return; // c0 and ld are multiples of 32: whole warps leave
+    if (c >= c_end) return; // c0 and c_end are multiples of 32: whole warps leave
     const int nl = !LEFT ? 0 : ((c - lane) < c_split ? nleft_lo : nleft_hi); // warp-uniform
     const int fr = lane >> 2, fk = lane & 3;
     if (LEFT && nl > 0) {
@@ -632,6 +632,7 @@ static int g_gemm_mode = 1;
 // panel (one register-file-filling CTA per SM, 200 layers = 1.35 waves on 148 SMs) the trailing updates of the other
 // slices fill the idle SMs.
 static int g_lu_groups = 2;
+static int g_lu_lookahead = 1; // development switch RT_B200_LU_LOOKAHEAD=0: every group on one stream
 // 128-wide super-blocks (third blocking level, RT_B200_LU_SUPER=1).  Measured at N = 768, 200 layers: the 128-deep
 // trailing update reads and writes C half as often and runs at 2.47 instead of 2.87 ms per slab-iteration, but 4 GFLOP of
 // the update move into the TRSM's left update (0.68 -> 0.95 ms) and the panel's wider interchange costs 0.04 ms: 5.42 vs
@@ -693,25 +694,80 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
         launch_panel(d, st[g], k0, nleft, ga0[g], ga1[g]);
         rt_prof_end(m, c_panel, st[g]);
     };
-    // columns [k0+32, ld) right of the panel at k0: left update nleft_lo wide left of c_split, nleft_hi wide from c_split on
-    auto trsm = [&](int g, int k0, int nleft_lo, int nleft_hi, int c_split) {
-        const int c0 = k0 + 32;
-        const double nc = ld - c0, ncl = std::max(0, std::min(c_split, ld) - c0), nch = nc - ncl;
-        rt_prof_begin(m, c_trsm, st[g], 32. * 32. * nc + 2. * 32. * (nleft_lo * ncl + nleft_hi * nch),
+    // columns [c0, c1) right of the panel at k0: left update nleft_lo wide left of c_split, nleft_hi wide from c_split on
+    auto trsm_on = [&](cudaStream_t ss, int g, int k0, int c0, int c1, int nleft_lo, int nleft_hi, int c_split) {
+        const double nc = c1 - c0, ncl = std::max(0, std::min(c_split, c1) - c0), nch = nc - ncl;
+        rt_prof_begin(m, c_trsm, ss, 32. * 32. * nc + 2. * 32. * (nleft_lo * ncl + nleft_hi * nch),
                       16. * 32. * nc + 8. * (nleft_lo * ncl + nleft_hi * nch));
         g_rt_launches++;
-        const dim3 grid((ld - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]);
-        if (nleft_hi > 0) k_trsm<true><<<grid, TRSM_THREADS, trsm_smem_bytes(nleft_hi), st[g]>>>(d, k0, c0, nleft_lo, nleft_hi, c_split, ga0[g], ga1[g]);
-        else k_trsm<false><<<grid, TRSM_THREADS, 0, st[g]>>>(d, k0, c0, 0, 0, c_split, ga0[g], ga1[g]);
-        rt_prof_end(m, c_trsm, st[g]);
+        const dim3 grid((c1 - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]);
+        if (nleft_hi > 0) k_trsm<true><<<grid, TRSM_THREADS, trsm_smem_bytes(nleft_hi), ss>>>(d, k0, c0, c1, nleft_lo, nleft_hi, c_split, ga0[g], ga1[g]);
+        else k_trsm<false><<<grid, TRSM_THREADS, 0, ss>>>(d, k0, c0, c1, 0, 0, c_split, ga0[g], ga1[g]);
+        rt_prof_end(m, c_trsm, ss);
     };
-    auto gemm = [&](int g, int K, int i0, int kk0, int c0, int c1) {
+    auto trsm = [&](int g, int k0, int nleft_lo, int nleft_hi, int c_split) { trsm_on(st[g], g, k0, k0 + 32, ld, nleft_lo, nleft_hi, c_split); };
+    auto gemm_on = [&](cudaStream_t ss, int g, int K, int i0, int kk0, int c0, int c1) {
         const double mr = Np - i0, nc = c1 - c0;
-        rt_prof_begin(m, c_gemm, st[g], 2. * K * mr * nc, 16. * mr * nc + 8. * K * (mr + nc));
-        launch_gemm(d, st[g], K, i0, kk0, c0, c1, ga0[g], ga1[g]);
-        rt_prof_end(m, c_gemm, st[g]);
+        rt_prof_begin(m, c_gemm, ss, 2. * K * mr * nc, 16. * mr * nc + 8. * K * (mr + nc));
+        launch_gemm(d, ss, K, i0, kk0, c0, c1, ga0[g], ga1[g]);
+        rt_prof_end(m, c_gemm, ss);
     };
+    auto gemm = [&](int g, int K, int i0, int kk0, int c0, int c1) { gemm_on(st[g], g, K, i0, kk0, c0, c1); };
     auto set_layers = [&](int g) { m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1); };
+    // LOOK-AHEAD schedule (default): per group a second stream T takes everything that is not on the critical path of
+    // the next block -- the TRSM of the first panel on the far columns and the trailing update right of the NEXT
+    // block's 64 columns -- so the next block's panels (latency-bound, a few SMs) start as soon as their own 64 columns
+    // are up to date and run beside the bulk of the trailing update:
+    //   S: panel(k0)  trsm [k0+32,k0+64)  gemm32  panel(k0+32)  ..wait T..  trsm2 [k0+64,ld)  gemm64 [k0+64,k0+128)  panel(k0+64) ...
+    //   T:            trsm [k0+64,ld)                                                       gemm64 [k0+128,ld)    trsm [k0+128,ld) ...
+    // With few active layers (the tail of a solve: every launch is far from filling the GPU) the chain of one block
+    // shrinks from panel+trsm+gemm32+panel+trsm+gemm64 to panel+trsm(32 columns)+gemm32+panel+trsm+gemm64(64 columns).
+    if (g_lu_lookahead && !g_lu_super && !m->prof_timing) {
+        bool ok = true;
+        for (int g = 0; g < G && ok; g++) {
+            if (m->lu_side[g]) continue;
+            ok = cudaStreamCreateWithFlags(&m->lu_side[g], cudaStreamNonBlocking) == cudaSuccess;
+            for (int e = 0; e < 3 && ok; e++) ok = cudaEventCreateWithFlags(&m->lu_ev[e][g], cudaEventDisableTiming) == cudaSuccess;
+        }
+        if (ok) {
+            for (int k0 = 0; k0 < Np; k0 += 64) {
+                for (int g = 0; g < G; g++) {
+                    cudaStream_t S = st[g], T = m->lu_side[g];
+                    set_layers(g);
+                    panel(g, k0, 0);
+                    if (k0 + 32 >= Np) { trsm_on(S, g, k0, k0 + 32, ld, 0, 0, ld); continue; }
+                    trsm_on(S, g, k0, k0 + 32, k0 + 64, 0, 0, ld);
+                    cudaEventRecord(m->lu_ev[0][g], S);
+                    cudaStreamWaitEvent(T, m->lu_ev[0][g], 0);
+                    trsm_on(T, g, k0, k0 + 64, ld, 0, 0, ld);
+                    cudaEventRecord(m->lu_ev[1][g], T);
+                    gemm_on(S, g, 32, k0 + 32, k0, k0 + 32, k0 + 64);
+                }
+                if (k0 + 32 >= Np) break;
+                for (int g = 0; g < G; g++) {
+                    cudaStream_t S = st[g], T = m->lu_side[g];
+                    set_layers(g);
+                    panel(g, k0 + 32, 32);
+                    cudaStreamWaitEvent(S, m->lu_ev[1][g], 0);
+                    trsm_on(S, g, k0 + 32, k0 + 64, ld, 32, 32, ld);
+                    if (k0 + 64 < Np) {
+                        const int cmid = std::min(k0 + 128, ld);
+                        gemm_on(S, g, 64, k0 + 64, k0, k0 + 64, cmid);
+                        if (cmid < ld) {
+                            cudaEventRecord(m->lu_ev[2][g], S);
+                            cudaStreamWaitEvent(T, m->lu_ev[2][g], 0);
+                            gemm_on(T, g, 64, k0 + 64, k0, cmid, ld);
+                        }
+                    }
+                }
+            }
+            for (int g = 0; g < G; g++) { // the back substitution (on S) needs the far columns (right-hand side) of T
+                cudaEventRecord(m->lu_ev[1][g], m->lu_side[g]);
+                cudaStreamWaitEvent(st[g], m->lu_ev[1][g], 0);
+            }
+            goto back_substitution;
+        }
+    }
     // Three blocking levels: panels of 32 columns inside blocks of 64 inside SUPER-BLOCKS of 128 (g_lu_super; while at
     // least 128 columns remain).  Inside a super-block at k0 the update of the columns right of it is deferred: the
     // four panels' TRSMs subtract the pending part L_left U themselves (32 rows each), the block-level update touches
@@ -750,6 +806,7 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
         }
         k0 += 128;
     }
+back_substitution:
     for (int g = 0; g < G; g++) {
         m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1);
         rt_prof_begin(m, c_back, st[g], (double)Np * Np, 4. * Np * Np);
@@ -771,6 +828,7 @@ cudaError_t lu_kernels_init()
     if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switches
     if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
     if (const char* gs = getenv("RT_B200_LU_SUPER")) g_lu_super = atoi(gs);
+    if (const char* gl = getenv("RT_B200_LU_LOOKAHEAD")) g_lu_lookahead = atoi(gl);
     const int sm128 = (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double), sm64 = (64 * 68 + 64 * GM_LDB) * (int)sizeof(double);
     const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
     cudaError_t e = cudaFuncSetAttribute(k_panel<1, 256>, at, 256 * 33 * (int)sizeof(double));

@@ -370,6 +370,10 @@ extern "C" rt_status rt_model_destroy(rt_model* m)
     for (auto& e : m->ev_pool) cudaEventDestroy(e);
     for (auto& e : m->timer_ev) if (e) cudaEventDestroy(e);
     if (m->h_n_active) cudaFreeHost(m->h_n_active);
+    for (int g = 0; g < RT_LU_MAX_GROUPS; g++) {
+        if (m->lu_side[g]) cudaStreamDestroy(m->lu_side[g]);
+        for (int e = 0; e < 3; e++) if (m->lu_ev[e][g]) cudaEventDestroy(m->lu_ev[e][g]);
+    }
     for (int g = 1; g < RT_LU_MAX_GROUPS; g++) {
         if (m->lu_streams[g]) cudaStreamDestroy(m->lu_streams[g]);
         if (m->lu_join[g]) cudaEventDestroy(m->lu_join[g]);

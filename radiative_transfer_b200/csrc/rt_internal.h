@@ -86,6 +86,8 @@ struct rt_model {
     cudaStream_t stream = nullptr;
     cudaStream_t lu_streams[RT_LU_MAX_GROUPS] = {};  // side streams of the grouped LU ([0] unused: group 0 runs on `stream`)
     cudaEvent_t lu_fork = nullptr, lu_join[RT_LU_MAX_GROUPS] = {};
+    cudaStream_t lu_side[RT_LU_MAX_GROUPS] = {};     // look-ahead: far-column work of every group
+    cudaEvent_t lu_ev[3][RT_LU_MAX_GROUPS] = {};
     int* h_n_active = nullptr;     // pinned
     bool has_cloud = false;
     bool use_fused = true;         // persistent one-CTA-per-layer solver when the matrix fits in shared memory
