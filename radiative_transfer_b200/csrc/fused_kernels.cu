@@ -184,8 +184,12 @@ __device__ __forceinline__ void reg_update(double (&a)[NQ][NS], const double (&l
 // Steps 8 KB .. 8 KB + 7, one CTA barrier per step; the publications (multipliers + pivot row) are double-buffered by
 // column parity.  Measured alternatives, all slower or equal on B200 (OH N = 56, per iteration): warps decoupled through
 // per-step mbarriers so that the rank-1 updates trail behind the pivot chain: 30 us vs 31 us; spinning on a shared-memory
-// counter instead of mbarriers: 155 us; speculative reciprocals of every lane's candidate: slower.  The step is bound by the
-// instruction count of the warp that searches the pivot (~3 cycles per dependent instruction), not by the barrier.
+// counter instead of mbarriers: 155 us; speculative reciprocals of every lane's candidate: slower; columns BLOCKED by warps
+// (warp w owns 8 consecutive columns and factors its sub-panel alone, warp-synchronously; the others apply the 8 pivots after
+// ONE barrier: 8 barriers per factorisation instead of 64, bitwise the same factors): 71.1 vs 72.0 ms per OH solve, i.e.
+// equal -- ncu then shows the owner warp's factorisation alone covering 74 % of the wall time at ~180 instructions and
+// ~700 cycles per column.  The step is bound by the instruction count of the warp that searches the pivot (~3-4 cycles per
+// dependent instruction of a single warp), not by the barrier.
 template <int NQ, int NS, int KB>
 __device__ __forceinline__ void reg_lu_block(double (&a)[NQ][NS], double (&b)[NQ], unsigned& done, double* M, int ldm, short* s_row,
                                              double* s_l, int (*s_pv)[4], int w, int lane)
