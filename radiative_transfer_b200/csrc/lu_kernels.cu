@@ -448,8 +448,8 @@ __global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trs
 // NST stages of K columns each (kk0, kk0 + K, ...): the accumulators stay in registers across the stages, so a 128-deep
 // update (K = 64, NST = 2) reads and writes C once -- half the C traffic per flop of two 64-deep updates -- while the
 // A / B tiles of one stage still fit three CTAs per SM.
-template <int K, int ROWS, int NST>
-__global__ void __launch_bounds__(ROWS * 2, (ROWS == 64 ? 3 : 2)) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
+template <int K, int ROWS, int NST, int MINB = (ROWS == 64 ? 3 : 2)>
+__global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
     const int a = a0 + blockIdx.z;
     if (a >= a1 || a >= *d.n_active) return;
@@ -621,12 +621,16 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
     else k_panel<PNL_BIG_R, PNL_BIG_NT><<<n, PNL_BIG_NT, smem, s>>>(d, k0, nleft, a0, a1);
 }
 
-// 0: 128x64 tiles, 2 CTAs/SM; 1 (default): 64x64 tiles, 3 CTAs/SM -- 3 % faster at N = 768.  A persistent, cp.async
+// 64-deep trailing update.  0: 128x64 tiles, one 64-deep stage, 2 CTAs/SM (2.97 ms per N = 768 slab-iteration);
+// 1: 64x64 tiles, one stage, 3 CTAs/SM (2.87 ms); 3 (default): 64x64 tiles, TWO 32-deep stages through one 36 KB buffer
+// and 128 registers -> FOUR CTAs/SM (2.59 ms): with the update at the machine balance of L2 and the tensor pipe, a fourth
+// resident CTA covers more of the others' load / store phases than the second barrier pair costs (five CTAs/SM at 96
+// registers spill: 2.64 ms).  A persistent, cp.async
 // double-buffered variant with C prefetch was measured 25 % SLOWER (3.6 vs 2.9 ms per slab-iteration): at K = 64 the
 // update moves 224 KB per tile through L2 for 4 us of DMMA work, i.e. ~8 TB/s chip-wide -- it is L2-bandwidth-bound,
 // not latency-bound, so deeper pipelining does not help.  A second attempt -- K cut into stages of 32, cp.async double
 // buffering inside the CTA, still 3 CTAs/SM -- was also slower (2.54 vs 2.47 ms at K = 128, 3.14 vs 2.88 ms at K = 64).
-static int g_gemm_mode = 1;
+static int g_gemm_mode = 3;
 // Layer groups of one solve (development switch RT_B200_LU_GROUPS).  The layers of a batch are independent, so the
 // active list is cut into G slices whose factorisations run on G streams: while one slice sits in a latency-bound
 // panel (one register-file-filling CTA per SM, 200 layers = 1.35 waves on 148 SMs) the trailing updates of the other
@@ -652,7 +656,8 @@ static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk
     if (K == 32) k_gemm<32, 128, 1><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
     else if (K == 64) {
         if (g_gemm_mode == 0) k_gemm<64, 128, 1><<<grid, 256, sm128, s>>>(d, i0, kk0, c0, c1, a0, a1);
-        else k_gemm<64, 64, 1><<<g64, 128, sm64, s>>>(d, i0, kk0, c0, c1, a0, a1);
+        else if (g_gemm_mode == 1) k_gemm<64, 64, 1><<<g64, 128, sm64, s>>>(d, i0, kk0, c0, c1, a0, a1);
+        else k_gemm<32, 64, 2, 4><<<g64, 128, (64 * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
     }
     else {
         if (g_gemm_mode == 0) k_gemm<64, 128, 2><<<grid, 256, sm128, s>>>(d, i0, kk0, c0, c1, a0, a1);
