@@ -61,7 +61,9 @@ __device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
 // scheduler; 400 instructions per column at 3 rows per thread, of which 82 DFMA on the 32-wide row and 48 LDS of the
 // pivot row; 62 us per m = 768 panel against 45 us now).  Measured alternatives, not kept: one barrier per column (each
 // warp's local winner publishes its candidate row; equal), 384 threads x 2 rows for m > 512 (equal), rows loaded straight
-// into registers instead of through the staging tile (6 % slower).
+// into registers instead of through the staging tile (6 % slower), 512 threads x 1 row for 256 < m <= 512 (4 % slower).
+// For 256 < m <= 384 the kernel runs as 192 threads x 2 rows: 168 registers keep TWO CTAs per SM, so 200 layers are one
+// wave instead of two (1.21 -> 1.16 ms per N = 768 slab-iteration, 0.46 -> 0.41 ms at N = 411).
 // Here the 32 columns are factored as four SUB-PANELS of 8 columns: inside a
 // sub-panel a column step touches only the 8 sub-panel columns of every row (<= 7 DFMA per row, 4 LDS, the pivot
 // row published as 8 doubles); the 24 (16, 8) columns to the right are updated once per sub-panel by a dense rank-8
@@ -92,7 +94,7 @@ __device__ __forceinline__ void panel_rank8(double (&x)[R][32], const double* __
 }
 
 template <int R, int NT>
-__global__ void __launch_bounds__(NT, (R == 1 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int a0, int a1)
+__global__ void __launch_bounds__(NT, (R * NT <= 384 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int a0, int a1)
 {
     const int a = a0 + blockIdx.x;
     if (a >= a1 || a >= *d.n_active) return;
@@ -610,6 +612,7 @@ __global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int a0, in
 // ------------------------------------------------------------------------------------------------------------
 // host driver
 // ------------------------------------------------------------------------------------------------------------
+static int g_panel_192 = 1; // development switch RT_B200_PANEL_192
 // Every launch works on the slice [a0, a1) of the compacted active list.
 static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, int a0, int a1)
 {
@@ -617,6 +620,7 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
     g_rt_launches++;
     const size_t smem = (size_t)m * 33 * sizeof(double);
     if (m <= 256) k_panel<1, 256><<<n, 256, smem, s>>>(d, k0, nleft, a0, a1);
+    else if (m <= 384 && g_panel_192) k_panel<2, 192><<<n, 192, smem, s>>>(d, k0, nleft, a0, a1); // 170 registers: still two CTAs per SM
     else if (m <= 512) k_panel<2, 256><<<n, 256, smem, s>>>(d, k0, nleft, a0, a1);
     else k_panel<PNL_BIG_R, PNL_BIG_NT><<<n, PNL_BIG_NT, smem, s>>>(d, k0, nleft, a0, a1);
 }
@@ -834,11 +838,13 @@ cudaError_t lu_kernels_init()
     if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switches
     if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
     if (const char* gs = getenv("RT_B200_LU_SUPER")) g_lu_super = atoi(gs);
+    if (const char* gp = getenv("RT_B200_PANEL_192")) g_panel_192 = atoi(gp);
     if (const char* gl = getenv("RT_B200_LU_LOOKAHEAD")) g_lu_lookahead = atoi(gl);
     const int sm128 = (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double), sm64 = (64 * 68 + 64 * GM_LDB) * (int)sizeof(double);
     const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
     cudaError_t e = cudaFuncSetAttribute(k_panel<1, 256>, at, 256 * 33 * (int)sizeof(double));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<2, 256>, at, 512 * 33 * (int)sizeof(double));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<2, 192>, at, 384 * 33 * (int)sizeof(double));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<PNL_BIG_R, PNL_BIG_NT>, at, 768 * 33 * (int)sizeof(double));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm<true>, at, (int)trsm_smem_bytes(96));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 128, 1>, at, sm128);
