@@ -176,9 +176,14 @@ __global__ void __launch_bounds__(NT, (R * NT <= 384 ? 2 : 1)) k_panel(DevModel 
                 if (lane == 0) s_key[buf][warp] = ((unsigned long long)mhi << 32) | mlo;
             }
             __syncthreads();
-            key = s_key[buf][0];
-#pragma unroll
-            for (int w = 1; w < NT / 32; w++) { const unsigned long long kk = s_key[buf][w]; key = kk > key ? kk : key; }
+            {   // max over the warps' keys: one load per lane + two REDUX instead of NT/32 loads and a compare chain
+                const unsigned long long kk = lane < NT / 32 ? s_key[buf][lane] : 0ull;
+                const unsigned hi = (unsigned)(kk >> 32);
+                const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+                const unsigned lo = hi == mhi ? (unsigned)kk : 0u;
+                const unsigned mlo = __reduce_max_sync(0xffffffffu, lo);
+                key = ((unsigned long long)mhi << 32) | mlo;
+            }
             const int p = j + 1023 - (int)(key & 0x3FFull);
             // ---- (2) interchange of positions j <-> p: the pivot row publishes its sub-panel columns, nothing else moves
 #pragma unroll
