@@ -653,7 +653,7 @@ static int g_lu_lookahead = 1; // development switch RT_B200_LU_LOOKAHEAD=0: eve
 // 5.52 ms per full-batch iteration, and SLOWER with few active layers (60 layers: 2.43 vs 2.35 ms), so the converged
 // CH3OH solve takes 210 instead of 207 ms.  Off by default; kept as a tested switch (tests/test_gpu_parity.py).
 static int g_lu_super = 0;
-#define LU_GROUP_MIN_LAYERS 48 // below this a slice no longer fills its share of the machine: fewer groups
+static int g_lu_group_min = 48; // layers per slice below which a slice no longer fills its share of the machine: fewer groups
 
 // K = 32: next panel's columns; 64: trailing update of a 64-wide block; 128: of a 128-wide super-block (two 64-deep stages)
 static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk0, int c0, int c1, int a0, int a1)
@@ -682,7 +682,7 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
     const int c_panel = rt_prof_class(m, "lu_panel"), c_trsm = rt_prof_class(m, "lu_trsm");
     const int c_gemm = rt_prof_class(m, "lu_gemm"), c_back = rt_prof_class(m, "lu_backsolve");
     // per-class event timing needs the launches of a class back to back on one stream: one group when profiling
-    int G = m->prof_timing ? 1 : std::min(g_lu_groups, std::max(1, bound / LU_GROUP_MIN_LAYERS));
+    int G = m->prof_timing ? 1 : std::min(g_lu_groups, std::max(1, bound / g_lu_group_min));
     G = std::min(G, RT_LU_MAX_GROUPS);
     if (G > 1 && !m->lu_streams[1]) {
         for (int g = 1; g < RT_LU_MAX_GROUPS; g++) {
@@ -844,6 +844,7 @@ cudaError_t lu_kernels_init()
     if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
     if (const char* gs = getenv("RT_B200_LU_SUPER")) g_lu_super = atoi(gs);
     if (const char* gp = getenv("RT_B200_PANEL_192")) g_panel_192 = atoi(gp);
+    if (const char* gq = getenv("RT_B200_LU_GROUP_MIN")) g_lu_group_min = std::max(1, atoi(gq));
     if (const char* gl = getenv("RT_B200_LU_LOOKAHEAD")) g_lu_lookahead = atoi(gl);
     const int sm128 = (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double), sm64 = (64 * 68 + 64 * GM_LDB) * (int)sizeof(double);
     const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
