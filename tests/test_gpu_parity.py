@@ -288,6 +288,39 @@ def test_full_size_oh_overlap_properties(solver_mod, best_checker):
             assert rel_err(pop[l], pop_o[0], 1e-30) < 1e-6
 
 
+def test_full_size_h2o_properties(solver_mod, best_checker):
+    """Config 4 (o-H2O, N = 411, L = 200, 7 collision tables incl. electrons, LU on DMMA with a 32-column remainder block):
+    one calc_new_pop of sampled layers against the oracle, normalisation, and full parity on layers that converge under
+    acceleration with margin (most layers of this synthetic slab do not: they are the retry policy's business)."""
+    from radiative_transfer_b200 import synthetic
+    p = synthetic.config_h2o(L=200)
+    m = solver_mod.Model(p)
+    b = m.boundary_layer_populations()
+    new, eq = m.calc_new_pop(b)
+    pop, st = m.calculate_populations()
+    m.close()
+    assert pop.shape == (200, 411)
+    assert np.allclose(b.sum(axis=1), 1.0, atol=1e-9) and np.allclose(new.sum(axis=1), 1.0, atol=1e-9)
+    assert np.allclose(pop.sum(axis=1), 1.0, atol=1e-9)
+    for l in (0, 101, 199):
+        q = p.sliced(l, l + 1)
+        b_o = best_checker.boundary(q)
+        assert rel_err(b[l], b_o[0], 1e-30) < 1e-8
+        new_o, eq_o = best_checker.step(q, b_o)
+        assert rel_err(new[l], new_o[0], 1e-30) < 1e-7
+    # Layers that need more than ~110 of the 150 accelerated iterations are marginal Ng iterations: rounding differences
+    # grow by ~20 % per iteration there (measured: 1e-9 agreement at 105 iterations, 1e-5 at 126-128 with identical
+    # iteration counts), so full parity is asserted on the layers that converge with a margin of 40 iterations.
+    solid = np.flatnonzero((st["converged"] == 1) & (st["iters"] < p.max_iter - 40))
+    assert solid.size >= 1
+    for l in solid[:2]:
+        q = p.sliced(int(l), int(l) + 1)
+        pop_o, st_o, _ = best_checker.solve(q)
+        assert st_o["converged"][0] == 1
+        assert abs(int(st_o["iters"][0]) - int(st["iters"][l])) <= 1
+        assert rel_err(pop[l], pop_o[0], 1e-30) < 1e-6
+
+
 @pytest.mark.gpu
 def test_super_block_lu_switch(problems):
     """RT_B200_LU_SUPER=1 (128-wide super-blocks, third blocking level of the LU; off by default, lu_kernels.cu): the
