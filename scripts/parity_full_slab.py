@@ -17,11 +17,16 @@ pop_o, st_o, _ = chk.solve(p, nthreads=os.cpu_count())
 dt = time.time() - t
 dit = np.abs(st["iters"].astype(int) - st_o["iters"].astype(int))
 both = (st["converged"] == 1) & (st_o["converged"] == 1)
-rel = np.zeros(p.L)
+rel = np.full(p.L, np.nan)
+bad = []
 for l in range(p.L):
-    big = pop_o[l] > 1e-30
+    big = np.isfinite(pop_o[l]) & (pop_o[l] > 1e-30)
+    if not big.any() or not np.isfinite(pop[l]).all():
+        bad.append(l)
+        continue
     rel[l] = np.max(np.abs(pop[l] - pop_o[l])[big] / pop_o[l][big])
-out = dict(config=cfg, N=int(p.N), L=int(p.L), checker=chk.kind, cpu_seconds=dt, threads=os.cpu_count(),
+both &= np.isfinite(rel)
+out = dict(layers_without_reference_answer=bad, config=cfg, N=int(p.N), L=int(p.L), checker=chk.kind, cpu_seconds=dt, threads=os.cpu_count(),
            flags_equal=int((st["converged"] == st_o["converged"]).sum()),
            iter_diff_le1=int((dit <= 1).sum()), iter_diff_max=int(dit.max()),
            layers_iter_diff_gt1=[(int(l), int(st["iters"][l]), int(st_o["iters"][l])) for l in np.flatnonzero(dit > 1)],
