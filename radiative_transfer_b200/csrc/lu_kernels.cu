@@ -640,7 +640,9 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
 // and 128 registers -> FOUR CTAs/SM (2.59 ms): with the update at the machine balance of L2 and the tensor pipe, a fourth
 // resident CTA covers more of the others' load / store phases than the second barrier pair costs (five CTAs/SM at 96
 // registers spill: 2.64 ms; 32 x 16 warp tiles, i.e. eight warps per CTA at 78 / 64 registers and three / four CTAs per
-// SM: 2.62 / 2.69 ms -- more resident warps than 16 per SM do not help).  A persistent, cp.async
+// SM: 2.62 / 2.69 ms -- more resident warps than 16 per SM do not help; the B tile kept resident over two row tiles,
+// 13 % less L2 traffic per flop at 53 KB / four CTAs per SM: 2.88 ms -- the longer serial life of a CTA costs more than the
+// traffic saves).  A persistent, cp.async
 // double-buffered variant with C prefetch was measured 25 % SLOWER (3.6 vs 2.9 ms per slab-iteration): at K = 64 the
 // update moves 224 KB per tile through L2 for 4 us of DMMA work, i.e. ~8 TB/s chip-wide -- it is L2-bandwidth-bound,
 // not latency-bound, so deeper pipelining does not help.  A second attempt -- K cut into stages of 32, cp.async double
