@@ -670,7 +670,9 @@ static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk
     const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, n);
     const size_t sm128 = (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), sm64 = (64 * 68 + 64 * GM_LDB) * sizeof(double);
     g_rt_launches++;
-    if (K == 32) k_gemm<32, 128, 1><<<grid, 256, (GM_ROWS * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
+    if (K == 32) { // next panel's 32 columns: 64 x 64 tiles at four CTAs/SM (128 x 64 at two: 0.5 % slower per slab-iteration)
+        k_gemm<32, 64, 1, 4><<<g64, 128, (64 * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
+    }
     else if (K == 64) {
         if (g_gemm_mode == 0) k_gemm<64, 128, 1><<<grid, 256, sm128, s>>>(d, i0, kk0, c0, c1, a0, a1);
         else if (g_gemm_mode == 1) k_gemm<64, 64, 1><<<g64, 128, sm64, s>>>(d, i0, kk0, c0, c1, a0, a1);
@@ -864,6 +866,6 @@ cudaError_t lu_kernels_init()
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 128, 2>, at, sm128);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 64, 1>, at, sm64);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 64, 2>, at, sm64);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 128, 1>, at, (GM_ROWS * 36 + 32 * GM_LDB) * (int)sizeof(double));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 4>, at, (64 * 36 + 32 * GM_LDB) * (int)sizeof(double));
     return e;
 }
