@@ -171,6 +171,14 @@ typedef struct rt_layer_soa {
      * scheme subclass reproduces it bit for bit.  NULL = derived from the fields above. */
     const double* vel_width;    /* [L] iteration_lvg.cpp:65; NULL: sqrt(2kT/m + vel_turb^2) */
     const double* partner_conc; /* [L][nb_neutral_tables + nb_electron_tables] coll_partn_conc of set_gas_param; NULL: species rule */
+    /* Optional (ABI 4): the cloud is a STACK of nb_models independent slabs of the same molecule (a parameter sweep solved
+     * as one batch): model k owns layers [model_first[k], model_first[k+1]).  Layers are independent, so this changes
+     * nothing for the independent-start modes; RT_START_CHAINED then runs the reference's warm-start chain
+     * (radiative_transfer.cpp:247-253) inside every model and advances layer l of ALL models together, one nb_models-wide
+     * batch per chain step, never chaining across a model boundary.  nb_models == 0 / NULL: one model of nb_lay layers. */
+    int nb_models;
+    int reserved0;
+    const int* model_first;     /* [nb_models + 1], model_first[0] == 0, ascending, model_first[nb_models] == nb_lay */
 } rt_layer_soa;
 
 /* Per-layer outcome == the public members of iteration_control after calculate_populations
@@ -224,7 +232,8 @@ rt_status rt_solve(rt_model* m, double* pop, int start_mode, int max_iter, doubl
 
 /* == calc_molecular_populations (radiative_transfer.cpp:219-289) incl. the retry policy (:259-276):
  * accelerated run with max_iter_acc, then for layers that failed and molecules other than CH3OHa/CH3OHe an
- * un-accelerated run with max_iter_ext.  start_mode RT_START_CHAINED reproduces the warm-start chain. */
+ * un-accelerated run with max_iter_ext.  start_mode RT_START_CHAINED reproduces the warm-start chain (one chain per
+ * model of a stacked cloud, see rt_layer_soa::model_first; chain step l of every model is one batch on the device). */
 rt_status rt_calc_molecular_populations(rt_model* m, double* pop, int start_mode, int acceleration,
                                         int max_iter_acc, int max_iter_ext, double min_err, rt_layer_status* st);
 

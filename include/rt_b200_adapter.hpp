@@ -228,15 +228,18 @@ inline void flatten_cloud(const cloud_data* cloud, flat_cloud& f)
     s.height = cloud->get_height();
 }
 
-// Drop-in for calc_molecular_populations (radiative_transfer.cpp:219-289).  start_mode RT_START_CHAINED reproduces the
-// reference's warm-start chain exactly (serial over layers); the default RT_START_BOUNDARY starts every layer from
-// boundary_layer_populations -- the reference's own start for layer 0 and after a failed layer (:250-253) -- and solves
-// all layers at once on the GPU.  Fatal conditions are reported like the reference does (message to cout) but return
-// false instead of exit(1).  max_iter_acc / max_iter_ext / min_err: MAX_NB_ITER_ACC, MAX_NB_ITER_EXT (:26-27),
-// rel_population_error (:45).
+// Drop-in for calc_molecular_populations (radiative_transfer.cpp:219-289).  The DEFAULT start_mode RT_START_CHAINED is the
+// reference's own semantics: layer l starts from the answer of layer l-1 when that one converged (:247-249), else from
+// boundary_layer_populations (:250-253); iterates, iteration counts and convergence flags are those of the unmodified
+// driver.  A single cloud is then a serial chain of one-layer solves (a sweep batches the chains of many clouds: stack
+// them with rt_layer_soa::model_first).  start_mode = RT_START_BOUNDARY is the explicit opt-in to the batch-parallel
+// independent start -- every layer from boundary_layer_populations, all layers at once on the GPU; same fixed points, but
+// NOT the driver's iterates: a layer with several solutions, or one that does not converge, can end elsewhere.
+// Fatal conditions are reported like the reference does (message to cout) but return false instead of exit(1).
+// max_iter_acc / max_iter_ext / min_err: MAX_NB_ITER_ACC, MAX_NB_ITER_EXT (:26-27), rel_population_error (:45).
 inline bool calc_molecular_populations_gpu(cloud_data* cloud, iteration_scheme_lvg* it_scheme_lvg, energy_diagram* mol_levels,
                                            einstein_coeff* mol_einst, collisional_transitions* mol_coll, double* mol_popul,
-                                           int nb_lev, bool acceleration, int verbosity, int start_mode = RT_START_BOUNDARY,
+                                           int nb_lev, bool acceleration, int verbosity, int start_mode = RT_START_CHAINED,
                                            int device = 0, int species_rule = -1, rt_layer_status* status = nullptr,
                                            int max_iter_acc = 150, int max_iter_ext = 15000, double min_err = 1.e-5)
 {

@@ -68,7 +68,8 @@ class rt_layer_soa(C.Structure):
     _fields_ = [("nb_lay", C.c_int), ("dust_ncomp", C.c_int)] + [
         (n, c_double_p) for n in ("temp_n", "temp_el", "el_conc", "h_conc", "ph2_conc", "oh2_conc", "he_conc",
                                   "mol_conc", "vel_turb", "velg_n", "dz", "vel_n", "dust_conc")
-    ] + [("height", C.c_double), ("vel_width", c_double_p), ("partner_conc", c_double_p)]
+    ] + [("height", C.c_double), ("vel_width", c_double_p), ("partner_conc", c_double_p),
+         ("nb_models", C.c_int), ("reserved0", C.c_int), ("model_first", c_int_p)]
 
 
 class rt_layer_status(C.Structure):
@@ -179,6 +180,16 @@ class Problem:
         for k, a in self.layers.items():
             lay[k] = a if k == "height" else np.ascontiguousarray(a[lo:hi])
         q.layers = lay
+        q.model_first = None  # a subset of a stack is a plain list of layers
+        return q
+
+    def take(self, idx) -> "Problem":
+        """Same model, the listed layers only, in the listed order (cyclic layer sharding)."""
+        import copy
+        idx = np.asarray(idx, dtype=np.int64)
+        q = copy.copy(self)
+        q.layers = {k: (a if k == "height" else np.ascontiguousarray(a[idx])) for k, a in self.layers.items()}
+        q.model_first = None
         return q
 
     # -- ctypes views ------------------------------------------------------------------------------------
@@ -242,4 +253,9 @@ class Problem:
                    "velg_n", "dz", "vel_n", "dust_conc"):
             a = np.ascontiguousarray(self.layers[nm], dtype=np.float64); hold.append(a); setattr(s, nm, dptr(a))
         s.height = float(self.layers["height"])
+        mf = getattr(self, "model_first", None)
+        if mf is not None:  # a stack of independent slabs (sharding.stack_clouds): one warm-start chain per model
+            a = np.ascontiguousarray(mf, dtype=np.int32); hold.append(a)
+            s.nb_models = a.shape[0] - 1
+            s.model_first = iptr(a)
         return s, hold

@@ -74,6 +74,23 @@ __global__ void k_set_active_failed(DevModel d, int lay_begin, int lay_end)
     if (lay < d.L) d.active_flag[lay] = (lay >= lay_begin && lay < lay_end && d.conv[lay] == 0) ? 1 : 0;
 }
 
+// the layers listed in d.lay_list[0..n) active, all others inactive (chain step l of every stacked model)
+__global__ void k_set_active_list(DevModel d, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) d.active_flag[d.lay_list[i]] = 1;
+}
+
+// warm start of the chain, radiative_transfer.cpp:247-249: pop[lay] <- pop[lay - 1] for the listed layers
+__global__ void k_copy_prev_pop(DevModel d, int n)
+{
+    const int i = blockIdx.y;
+    if (i >= n) return;
+    const int lay = d.lay_list[i];
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < d.N && lay > 0) d.pop[(size_t)lay * d.N + k] = d.pop[(size_t)(lay - 1) * d.N + k];
+}
+
 // boltzmann_populations, spectroscopy.cpp:1245-1259 (sequential partition sum, as the reference)
 __global__ void k_boltzmann(DevModel d)
 {
@@ -135,6 +152,19 @@ void launch_ctl_step(const DevModel& d, cudaStream_t s, int nlay_bound, int acce
 void launch_compact(const DevModel& d, cudaStream_t s) { g_rt_launches++; k_compact<<<1, 1024, 0, s>>>(d); }
 void launch_set_active_range(const DevModel& d, cudaStream_t s, int b, int e) { g_rt_launches++; k_set_active_range<<<(d.L + 255) / 256, 256, 0, s>>>(d, b, e); }
 void launch_set_active_failed(const DevModel& d, cudaStream_t s, int b, int e) { g_rt_launches++; k_set_active_failed<<<(d.L + 255) / 256, 256, 0, s>>>(d, b, e); }
+void launch_set_active_list(const DevModel& d, cudaStream_t s, int n)
+{
+    launch_set_active_range(d, s, 0, 0);
+    if (n <= 0) return;
+    g_rt_launches++;
+    k_set_active_list<<<(n + 255) / 256, 256, 0, s>>>(d, n);
+}
+void launch_copy_prev_pop(const DevModel& d, cudaStream_t s, int n)
+{
+    if (n <= 0) return;
+    g_rt_launches++;
+    k_copy_prev_pop<<<dim3((d.N + 255) / 256, n), 256, 0, s>>>(d, n);
+}
 void launch_boltzmann(const DevModel& d, cudaStream_t s) { g_rt_launches++; k_boltzmann<<<d.L, 256, 0, s>>>(d); }
 void launch_set_rhs(const DevModel& d, cudaStream_t s, int nlay_bound)
 {

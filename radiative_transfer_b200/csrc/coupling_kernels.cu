@@ -92,11 +92,20 @@ __device__ __forceinline__ void rate_electrons(const DevModel& d, int lay, int u
 // grid (ceil(N/32), ceil(N/32), L), block (32, 8): tile (bi, bj) of the lower triangle; writes C[i][j] = up-rate
 // j->i and, through a shared-memory transpose, C[j][i] = down-rate i->j, both as coalesced row segments.
 // half_A != 0: boundary_layer_populations variant (iteration_control.cpp:72-78): neutrals only, + 0.5*A_ul.
-__global__ void __launch_bounds__(256) k_coll_offdiag(DevModel d, double* __restrict__ out, int ldo, int half_A,
-                                                      const double* __restrict__ einst)
+// Layers: lay0 + blockIdx.z, or (bound > 0) the entries lay0 + blockIdx.z < min(bound, *n_active) of the compacted active list.
+__device__ __forceinline__ int coll_layer(const DevModel& d, int idx, int bound)
 {
-    const int bi = blockIdx.y, bj = blockIdx.x, lay = blockIdx.z;
+    if (bound <= 0) return idx < d.L ? idx : -1;
+    return (idx < bound && idx < *d.n_active) ? d.active[idx] : -1;
+}
+
+__global__ void __launch_bounds__(256) k_coll_offdiag(DevModel d, double* __restrict__ out, int ldo, int half_A,
+                                                      const double* __restrict__ einst, int lay0, int bound)
+{
+    const int bi = blockIdx.y, bj = blockIdx.x;
     if (bj > bi) return;
+    const int lay = coll_layer(d, lay0 + blockIdx.z, bound);
+    if (lay < 0) return;
     __shared__ double s_down[32][33];
     double* C = out + (size_t)lay * d.Np * ldo;
     const int tx = threadIdx.x, ty = threadIdx.y;
@@ -125,11 +134,11 @@ __global__ void __launch_bounds__(256) k_coll_offdiag(DevModel d, double* __rest
 
 // Diagonal = -(sum of the other entries of the column) (iteration_lvg.cpp:127-131: every rate leaves its source
 // level through the diagonal of the source column); padding block = identity.  One thread per column, coalesced.
-__global__ void k_coll_diag(DevModel d, double* __restrict__ out, int ldo)
+__global__ void k_coll_diag(DevModel d, double* __restrict__ out, int ldo, int lay0, int bound)
 {
-    const int lay = blockIdx.y;
+    const int lay = coll_layer(d, lay0 + blockIdx.y, bound);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= d.Np) return;
+    if (lay < 0 || i >= d.Np) return;
     double* C = out + (size_t)lay * d.Np * ldo;
     if (i >= d.N) {
         for (int r = 0; r < d.Np; r++) C[(size_t)r * ldo + i] = (r == i) ? 1. : 0.;
@@ -142,16 +151,23 @@ __global__ void k_coll_diag(DevModel d, double* __restrict__ out, int ldo)
     for (int r = d.N; r < d.Np; r++) C[(size_t)r * ldo + i] = 0.;
 }
 
-void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int half_A)
+// bound <= 0: every layer of the cloud; bound > 0: the first `bound` entries of the compacted active list (the start
+// vectors of a chained solve or of the retry pass touch only the layers they are for).  Layers ride in gridDim.z / .y,
+// which the hardware caps at 65535: larger (stacked) clouds go in chunks.
+void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int half_A, int bound)
 {
     const int ldo = (out == d.Mmat) ? d.ld : d.Np; // the boundary-start variant assembles straight into Mmat
     const int nt = (d.N + 31) / 32;
-    dim3 grid(nt, nt, d.L), block(32, 8);
-    g_rt_launches++;
-    k_coll_offdiag<<<grid, block, 0, s>>>(d, out, ldo, half_A, d.einst);
-    dim3 g2((d.Np + 127) / 128, d.L);
-    g_rt_launches++;
-    k_coll_diag<<<g2, 128, 0, s>>>(d, out, ldo);
+    const int nl = bound > 0 ? bound : d.L;
+    for (int lay0 = 0; lay0 < nl; lay0 += 65535) {
+        const int n = nl - lay0 < 65535 ? nl - lay0 : 65535;
+        dim3 grid(nt, nt, n), block(32, 8);
+        g_rt_launches++;
+        k_coll_offdiag<<<grid, block, 0, s>>>(d, out, ldo, half_A, d.einst, lay0, bound);
+        dim3 g2((d.Np + 127) / 128, n);
+        g_rt_launches++;
+        k_coll_diag<<<g2, 128, 0, s>>>(d, out, ldo, lay0, bound);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------

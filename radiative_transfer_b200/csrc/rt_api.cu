@@ -108,7 +108,7 @@ const char* rt_status_string(rt_status s)
 }
 
 const char* rt_last_error(const rt_model* m) { return m ? m->last_error.c_str() : g_create_error.c_str(); }
-int rt_abi_version(void) { return 3; }
+int rt_abi_version(void) { return 4; }
 
 } // extern "C"
 
@@ -445,11 +445,21 @@ static int coll_locate(const double* tgrid, int jmax, double temp)
 extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
 {
     if (!m || !lay || lay->nb_lay < 1) return RT_ERR_INVALID;
+    m->last_error.clear(); // errors are per call: a recoverable error of an earlier call must not fail this one
+    if (lay->nb_lay > 65535) { m->last_error = "more than 65535 layers in one cloud (layers ride in gridDim.y): split the stack"; return RT_ERR_UNSUPPORTED; }
     if (lay->dust_ncomp != m->d.ncomp) { m->last_error = "inconsistency in the interstellar dust data"; return RT_ERR_DUST_INCONSISTENT; }
+    std::vector<int> chain_first = {0, lay->nb_lay};
+    if (lay->nb_models > 0) {
+        bool ok = lay->model_first && lay->model_first[0] == 0 && lay->model_first[lay->nb_models] == lay->nb_lay;
+        for (int k = 0; ok && k < lay->nb_models; k++) ok = lay->model_first[k + 1] > lay->model_first[k];
+        if (!ok) { m->last_error = "rt_layer_soa::model_first must ascend from 0 to nb_lay"; return RT_ERR_INVALID; }
+        chain_first.assign(lay->model_first, lay->model_first + lay->nb_models + 1);
+    }
     CK(cudaSetDevice(m->device));
     CK(cudaStreamSynchronize(m->stream));
     DevModel& d = m->d;
     const int L = lay->nb_lay, N = d.N, Np = d.Np, K = d.K;
+    m->chain_first = chain_first;
     m->cloud_reuse = m->has_cloud && d.L == L;
     m->cloud_slot = 0;
     if (!m->cloud_reuse) free_cloud(m);
@@ -523,6 +533,7 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
     for (double** p : dp) *p = dev_alloc<double>(m, L, true);
     d.eq_bits = dev_alloc<unsigned long long>(m, L, true);
     d.n_active = dev_alloc<int>(m, 4, true);
+    d.lay_list = dev_alloc<int>(m, L, true);
     if (!d.Cmat || !d.Mmat || !d.pop || !d.hist_pop || !d.hist_res || !d.n_active || !m->last_error.empty()) {
         m->cloud_reuse = false;
         free_cloud(m);
@@ -541,6 +552,7 @@ extern "C" rt_status rt_cloud_upload(rt_model* m, const rt_layer_soa* lay)
 extern "C" rt_status rt_cloud_rebuild(rt_model* m)
 {
     if (!m) return RT_ERR_INVALID;
+    m->last_error.clear();
     if (!m->has_cloud) { m->last_error = "no cloud uploaded"; return RT_ERR_NO_CLOUD; }
     CK(cudaSetDevice(m->device));
     const DevModel& d = m->d;
@@ -585,7 +597,7 @@ static void enqueue_start(rt_model* m, int start_mode, int bound)
         double tab_bytes = 0.;
         for (int k = 0; k < d.nb1; k++) tab_bytes += 16. * d.tab[k].imax;
         rt_prof_begin(m, c0, s, 0., tab_bytes + 12. * d.N * d.N);
-        launch_coll_matrix(d, s, d.Mmat, 1);
+        launch_coll_matrix(d, s, d.Mmat, 1, bound); // only the layers this start is for
         rt_prof_end(m, c0, s);
         launch_set_row0(d, s, bound);
         launch_set_rhs(d, s, bound);
@@ -595,18 +607,18 @@ static void enqueue_start(rt_model* m, int start_mode, int bound)
     else if (start_mode == RT_START_LTE) launch_boltzmann(d, s);
 }
 
-// iteration_control::calculate_populations for layers [lb, le) (or only the non-converged ones of that range)
-static rt_status solve_range(rt_model* m, int lb, int le, int start_mode, int max_iter, double min_err, int accel, bool only_failed)
+// iteration_control::calculate_populations for the layers whose active_flag is set (the caller flagged them: a range,
+// the failed layers of a range, or an explicit list); `n_flagged_hint` layers at most
+static rt_status solve_flagged(rt_model* m, int start_mode, int max_iter, double min_err, int accel)
 {
     const DevModel& d = m->d;
     cudaStream_t s = m->stream;
-    if (only_failed) launch_set_active_failed(d, s, lb, le);
-    else launch_set_active_range(d, s, lb, le);
     launch_compact(d, s);
     CK(cudaMemcpyAsync(m->h_n_active, d.n_active, sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     int bound = m->h_n_active[0];
     if (bound == 0) return RT_OK;
+    const int n_layers = bound;
     m->prof_layers = bound;
     enqueue_start(m, start_mode, bound);
     launch_ctl_init_flagged(d, s, accel);
@@ -618,17 +630,19 @@ static rt_status solve_range(rt_model* m, int lb, int le, int start_mode, int ma
         rt_prof_end(m, c_f, s);
         CK(cudaStreamSynchronize(s));
         CK(cudaGetLastError());
-        std::vector<int> itn(d.L);
+        // the active list is untouched by the fused kernel: it still names the layers of this solve
+        std::vector<int> itn(d.L), act(n_layers);
         CK(cudaMemcpy(itn.data(), d.iter_nb, sizeof(int) * d.L, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(act.data(), d.active, sizeof(int) * n_layers, cudaMemcpyDeviceToHost));
         int mx = 0;
         double layer_iters = 0.;
-        for (int l = lb; l < le; l++) { mx = std::max(mx, itn[l]); layer_iters += itn[l]; }
+        for (int l : act) { mx = std::max(mx, itn[l]); layer_iters += itn[l]; }
         m->iters_enqueued += mx;
         // algorithmic work of the launch, known only now: per layer-iteration one LU + two triangular solves +
         // the residual product; HBM bytes only when C(layer) does not fit beside M in shared memory (Np > 96)
         const double n = d.N;
         m->prof_flops[c_f] += layer_iters * (2. / 3. * n * n * n + 4. * n * n);
-        m->prof_bytes[c_f] += layer_iters * (d.Np > 96 ? 8. * n * n : 0.) + (double)(le - lb) * 8. * n * n;
+        m->prof_bytes[c_f] += layer_iters * (d.Np > 96 ? 8. * n * n : 0.) + (double)n_layers * 8. * n * n;
         return RT_OK;
     }
     const int c_ctl = rt_prof_class(m, "controller");
@@ -660,6 +674,46 @@ static rt_status solve_range(rt_model* m, int lb, int le, int start_mode, int ma
     return RT_OK;
 }
 
+// ... for layers [lb, le) (or only the non-converged ones of that range)
+static rt_status solve_range(rt_model* m, int lb, int le, int start_mode, int max_iter, double min_err, int accel, bool only_failed)
+{
+    if (only_failed) launch_set_active_failed(m->d, m->stream, lb, le);
+    else launch_set_active_range(m->d, m->stream, lb, le);
+    return solve_flagged(m, start_mode, max_iter, min_err, accel);
+}
+
+// flags <- the listed layers (host list -> d.lay_list -> active_flag)
+static rt_status flag_layers(rt_model* m, const std::vector<int>& lay)
+{
+    if (!lay.empty()) CK(cudaMemcpyAsync(m->d.lay_list, lay.data(), sizeof(int) * lay.size(), cudaMemcpyHostToDevice, m->stream));
+    launch_set_active_list(m->d, m->stream, (int)lay.size());
+    CK(cudaStreamSynchronize(m->stream)); // `lay` is pageable host memory that the caller may change next
+    return RT_OK;
+}
+
+// One attempt of one chain step (radiative_transfer.cpp:247-257 / :263-272): the listed layers get the populations of the
+// layer before them when that one converged (`warm`), boundary_layer_populations otherwise (`cold`), then iterate together.
+static rt_status chain_attempt(rt_model* m, const std::vector<int>& cold, const std::vector<int>& warm, int max_iter, double min_err, int accel)
+{
+    const DevModel& d = m->d;
+    rt_status r;
+    if (!cold.empty()) {
+        if ((r = flag_layers(m, cold))) return r;
+        launch_compact(d, m->stream);
+        m->prof_layers = (int)cold.size();
+        enqueue_start(m, RT_START_BOUNDARY, (int)cold.size());
+    }
+    if (!warm.empty()) {
+        CK(cudaMemcpyAsync(d.lay_list, warm.data(), sizeof(int) * warm.size(), cudaMemcpyHostToDevice, m->stream));
+        launch_copy_prev_pop(d, m->stream, (int)warm.size());
+        CK(cudaStreamSynchronize(m->stream));
+    }
+    std::vector<int> all(cold);
+    all.insert(all.end(), warm.begin(), warm.end());
+    if ((r = flag_layers(m, all))) return r;
+    return solve_flagged(m, RT_START_GIVEN, max_iter, min_err, accel);
+}
+
 static bool is_methanol(const rt_model* m) { return m->mol_name == "CH3OHa" || m->mol_name == "CH3OHe"; }
 
 static rt_status fetch_status(rt_model* m, rt_layer_status* st)
@@ -680,6 +734,7 @@ static rt_status fetch_status(rt_model* m, rt_layer_status* st)
 
 #define NEED_CLOUD()                                                   \
     if (!m) return RT_ERR_INVALID;                                     \
+    m->last_error.clear();                                             \
     if (!m->has_cloud) { m->last_error = "no cloud uploaded"; return RT_ERR_NO_CLOUD; } \
     CK(cudaSetDevice(m->device))
 
@@ -751,19 +806,34 @@ rt_status rt_calc_molecular_populations(rt_model* m, double* pop, int start_mode
         }
     }
     else {
-        // warm-start chain, radiative_transfer.cpp:236-281: layer l starts from layer l-1 if that one converged
-        int prev_found = 0;
-        for (int l = 0; l < L; l++) {
-            for (int attempt = 0; attempt < 2; attempt++) {
-                int sm = RT_START_BOUNDARY;
-                if (l > 0 && prev_found) {
-                    CK(cudaMemcpyAsync(d.pop + (size_t)l * N, d.pop + (size_t)(l - 1) * N, sizeof(double) * N, cudaMemcpyDeviceToDevice, m->stream));
-                    sm = RT_START_GIVEN;
+        // warm-start chain, radiative_transfer.cpp:236-281: layer l starts from layer l-1 if that one converged.  A stacked
+        // cloud (rt_layer_soa::model_first) holds one chain per model; chain step l of ALL models is one batch.
+        const std::vector<int>& first = m->chain_first;
+        const int nm = (int)first.size() - 1;
+        int maxlen = 0;
+        for (int k = 0; k < nm; k++) maxlen = std::max(maxlen, first[k + 1] - first[k]);
+        std::vector<int> prev_found(nm, 0), conv(L);
+        for (int step = 0; step < maxlen; step++) {
+            std::vector<int> cold, warm;
+            for (int k = 0; k < nm; k++) {
+                const int lay = first[k] + step;
+                if (lay >= first[k + 1]) continue;
+                (step > 0 && prev_found[k] ? warm : cold).push_back(lay);
+            }
+            if ((r = chain_attempt(m, cold, warm, iter_max, min_err, acceleration))) return r;
+            CK(cudaMemcpy(conv.data(), d.conv, sizeof(int) * L, cudaMemcpyDeviceToHost));
+            if (retry) { // the same kind of start once more, un-accelerated (:259-276)
+                std::vector<int> cold2, warm2;
+                for (int lay : cold) if (!conv[lay]) cold2.push_back(lay);
+                for (int lay : warm) if (!conv[lay]) warm2.push_back(lay);
+                if (!cold2.empty() || !warm2.empty()) {
+                    if ((r = chain_attempt(m, cold2, warm2, max_iter_ext, min_err, 0))) return r;
+                    CK(cudaMemcpy(conv.data(), d.conv, sizeof(int) * L, cudaMemcpyDeviceToHost));
                 }
-                if ((r = solve_range(m, l, l + 1, sm, attempt == 0 ? iter_max : max_iter_ext, min_err, attempt == 0 ? acceleration : 0, false))) return r;
-                int cv = 0;
-                CK(cudaMemcpy(&cv, d.conv + l, sizeof(int), cudaMemcpyDeviceToHost));
-                if (cv || !retry || attempt == 1) { prev_found = cv; break; }
+            }
+            for (int k = 0; k < nm; k++) {
+                const int lay = first[k] + step;
+                if (lay < first[k + 1]) prev_found[k] = conv[lay];
             }
         }
     }

@@ -70,6 +70,7 @@ struct DevModel {
     double *best_eq, *eq_err, *pop_err, *rel_err;
     unsigned long long* eq_bits; // [L] max |df| of the current assembly as ordered bits
     int *active, *n_active;  // compacted list of layers still iterating
+    int* lay_list;           // [L] scratch: an explicit list of layers handed down by the host (chained start)
 };
 
 struct rt_model {
@@ -80,6 +81,7 @@ struct rt_model {
     std::string last_error;
     std::vector<void*> allocs;     // every cudaMalloc, freed in rt_model_destroy
     std::vector<void*> cloud_allocs;
+    std::vector<int> chain_first;  // rt_layer_soa::model_first of the resident cloud ({0, L} for a single slab)
     bool cloud_reuse = false;      // rt_cloud_upload with an unchanged layer count hands the resident buffers out again
     size_t cloud_slot = 0;
     std::vector<std::vector<double>> h_tgrid; // host copy of the collision tables' temperature grids (set_gas_param)
@@ -121,7 +123,7 @@ extern long long g_rt_launches; // every kernel launch of the library (bench.py 
 
 // ---- kernel launchers (each returns after enqueueing on `s`) -------------------------------------------------
 // layers processed = active[0 .. min(*n_active, nlay_bound))
-void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int neutrals_only_half_A);
+void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int neutrals_only_half_A, int active_bound = 0);
 void launch_intensity(const DevModel& d, cudaStream_t s, int nlay_bound);
 void launch_assemble(const DevModel& d, cudaStream_t s, int nlay_bound, double* df_out /*[L][N] or null*/);
 void launch_lu_solve(rt_model* m, cudaStream_t s, int nlay_bound);
@@ -130,6 +132,8 @@ void launch_ctl_step(const DevModel& d, cudaStream_t s, int nlay_bound, int acce
 void launch_compact(const DevModel& d, cudaStream_t s);
 void launch_set_active_range(const DevModel& d, cudaStream_t s, int lay_begin, int lay_end);
 void launch_set_active_failed(const DevModel& d, cudaStream_t s, int lay_begin, int lay_end);
+void launch_set_active_list(const DevModel& d, cudaStream_t s, int n);   // flags <- d.lay_list[0..n)
+void launch_copy_prev_pop(const DevModel& d, cudaStream_t s, int n);     // pop[lay] <- pop[lay-1] for lay in d.lay_list[0..n)
 void launch_boltzmann(const DevModel& d, cudaStream_t s);
 void launch_set_rhs(const DevModel& d, cudaStream_t s, int nlay_bound);
 void launch_set_row0(const DevModel& d, cudaStream_t s, int nlay_bound);

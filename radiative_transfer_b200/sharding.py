@@ -25,33 +25,52 @@ def layer_range(L: int, world: int, rank: int) -> Tuple[int, int]:
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-def all_gather_layers(local, L: int, world: int, rank: int):
-    """local: torch tensor [l_rank, ...] on the backend's device.  Returns the [L, ...] tensor on every rank."""
+def layer_indices(L: int, world: int, rank: int, cyclic: bool = False) -> np.ndarray:
+    """Layers owned by `rank`.  Contiguous blocks (layer_range) keep the warm-start chain of the reference inside a rank
+    (radiative_transfer.cpp:247-249).  CYCLIC (layer l -> rank l mod world) is for the independent-start mode: iteration
+    counts vary smoothly along a slab (CH3OH: 16 -> 66), so a contiguous split leaves the rank that owns the slow end
+    working while the others idle; dealing the layers out round-robin gives every rank the same mix."""
+    if cyclic:
+        return np.arange(rank, L, world)
+    lo, hi = layer_range(L, world, rank)
+    return np.arange(lo, hi)
+
+
+def all_gather_layers(local, L: int, world: int, rank: int, cyclic: bool = False):
+    """local: torch tensor [l_rank, ...] on the backend's device (rows in the order of layer_indices).  Returns the
+    [L, ...] tensor in slab order on every rank: ONE all_gather of equal-size (padded) blocks."""
     import torch
     import torch.distributed as dist
-    sizes = [layer_range(L, world, r)[1] - layer_range(L, world, r)[0] for r in range(world)]
+    idx = [layer_indices(L, world, r, cyclic) for r in range(world)]
+    sizes = [len(i) for i in idx]
     assert local.shape[0] == sizes[rank]
     if world == 1:
         return local
     mx = max(sizes)
     pad = torch.zeros((mx,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
     pad[: sizes[rank]] = local
-    out = [torch.empty_like(pad) for _ in range(world)]
-    dist.all_gather(out, pad)
-    return torch.cat([o[:s] for o, s in zip(out, sizes)], dim=0)
+    out = torch.empty((world * mx,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, pad)
+    out = out.view((world, mx) + tuple(local.shape[1:]))
+    full = torch.empty((L,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    for r in range(world):
+        if sizes[r]:
+            full[torch.as_tensor(idx[r], device=local.device)] = out[r, : sizes[r]]
+    return full
 
 
-def solve_sharded(problem, solve_fn: Callable, world: int, rank: int, device=None):
+def solve_sharded(problem, solve_fn: Callable, world: int, rank: int, device=None, cyclic: bool = False):
     """Solves ONE slab with its layers partitioned over `world` ranks.
 
     solve_fn(sub_problem) -> (pop [l, N] float64 ndarray, status structured ndarray [l]) is the rank-local solver
     (radiative_transfer_b200.solver.Model(...).calc_molecular_populations on a GPU rank).  Returns the full
-    (pop [L, N], status [L]) on every rank."""
+    (pop [L, N], status [L]) on every rank.  cyclic: see layer_indices (independent-start modes only)."""
     import torch
     from . import abi
-    lo, hi = layer_range(problem.L, world, rank)
+    mine = layer_indices(problem.L, world, rank, cyclic)
+    lo, hi = 0, len(mine)
     if hi > lo:
-        pop, st = solve_fn(problem.sliced(lo, hi))
+        pop, st = solve_fn(problem.take(mine))
     else:
         pop, st = np.zeros((0, problem.N)), np.zeros(0, dtype=abi.STATUS_DTYPE)
     if world == 1:
@@ -61,8 +80,8 @@ def solve_sharded(problem, solve_fn: Callable, world: int, rank: int, device=Non
     # status as a float64 [l, 5] block so that one dtype travels
     st_t = torch.from_numpy(np.stack([st["iters"].astype(np.float64), st["converged"].astype(np.float64), st["eq_error"],
                                       st["pop_error"], st["rel_error"]], axis=1) if hi > lo else np.zeros((0, 5))).to(dev)
-    pop_all = all_gather_layers(pop_t, problem.L, world, rank).cpu().numpy()
-    st_all = all_gather_layers(st_t, problem.L, world, rank).cpu().numpy()
+    pop_all = all_gather_layers(pop_t, problem.L, world, rank, cyclic).cpu().numpy()
+    st_all = all_gather_layers(st_t, problem.L, world, rank, cyclic).cpu().numpy()
     out = np.zeros(problem.L, dtype=abi.STATUS_DTYPE)
     out["iters"] = st_all[:, 0].astype(np.int32); out["converged"] = st_all[:, 1].astype(np.int32)
     out["eq_error"], out["pop_error"], out["rel_error"] = st_all[:, 2], st_all[:, 3], st_all[:, 4]
@@ -87,10 +106,17 @@ class SweepQueue:
             solve(grid_point(i))
     """
 
+    _seq = {}  # sweeps constructed so far in this process, per name
+
     def __init__(self, n_points: int, name: str = "rt_sweep", store=None):
         import torch.distributed as dist
         self.n = int(n_points)
-        self.key = f"{name}/next"
+        # One counter per SWEEP: the k-th queue of a given name gets its own store key.  Every rank runs the same program
+        # (SPMD) and so constructs its queues in the same order; the k-th queue of every rank therefore shares one key,
+        # and a second sweep in the same process group starts from zero instead of from the first sweep's final count.
+        k = SweepQueue._seq.get(name, 0)
+        SweepQueue._seq[name] = k + 1
+        self.key = f"{name}/{k}/next"
         self._local = 0
         self.store = store
         if store is None and dist.is_available() and dist.is_initialized():
@@ -127,4 +153,5 @@ def stack_clouds(problems):
         ranges.append((lo, lo + q.L))
         lo += q.L
     base.layers = lay
+    base.model_first = np.array([r[0] for r in ranges] + [lo], dtype=np.int32)  # rt_layer_soa::model_first
     return base, ranges

@@ -237,6 +237,81 @@ def test_stacked_clouds_solve_like_separate_models(solver_mod):
         assert np.array_equal(pop[lo:hi], pop1) and np.array_equal(st["iters"][lo:hi], st1["iters"])
 
 
+def test_stacked_chained_start_one_chain_per_model(solver_mod, best_checker):
+    """RT_START_CHAINED on a stack of slabs (rt_layer_soa::model_first): the reference's warm-start chain
+    (radiative_transfer.cpp:236-281) runs inside every model, chain step l of all models as one batch, and never crosses a
+    model boundary: bitwise the per-model chained solves, which in turn match the reference's calc_molecular_populations."""
+    from radiative_transfer_b200 import abi, sharding, synthetic
+    kw = dict(n_vt=2, n_k=6, n_j=8)
+    models = [synthetic.config_ch3oh(L=5, **kw), synthetic.config_ch3oh(L=3, cloud_kw=dict(t_hi=180.0, nh_hi=3e7), **kw),
+              synthetic.config_ch3oh(L=6, cloud_kw=dict(t_hi=120.0, nh_hi=1e6, velg_scale=1e-11), **kw)]
+    s, ranges = sharding.stack_clouds(models)
+    assert s.model_first.tolist() == [0, 5, 8, 14]
+    m = solver_mod.Model(s)
+    pop, st = m.calc_molecular_populations(start_mode=abi.RT_START_CHAINED)
+    m.close()
+    for q, (lo, hi) in zip(models, ranges):
+        m1 = solver_mod.Model(q)
+        pop1, st1 = m1.calc_molecular_populations(start_mode=abi.RT_START_CHAINED)
+        m1.close()
+        assert np.array_equal(pop[lo:hi], pop1) and np.array_equal(st["iters"][lo:hi], st1["iters"])
+        pop_o, st_o, _ = best_checker.calc_molecular_populations(q)
+        assert np.array_equal(st1["converged"], st_o["converged"])
+        conv = st_o["converged"] == 1
+        assert np.all(np.abs(st1["iters"] - st_o["iters"])[conv] <= 1)
+        assert rel_err(pop1[conv], pop_o[conv], 1e-30) < 1e-6
+    # the chain really is a warm start: layers after the first need fewer iterations than from the boundary start
+    m = solver_mod.Model(models[0])
+    _, st_b = m.calculate_populations()
+    m.close()
+    assert st["iters"][1:5].sum() < st_b["iters"][1:5].sum()
+
+
+def test_chained_retry_non_methanol_stacked(solver_mod, best_checker, problems):
+    """Chain + retry policy (radiative_transfer.cpp:259-276) on a stack of two o-H2O-like slabs against the reference's own
+    calc_molecular_populations per model."""
+    from radiative_transfer_b200 import abi, sharding
+    a = problems("h2o_small", 3)
+    s, ranges = sharding.stack_clouds([a, a.sliced(1, 3)])
+    m = solver_mod.Model(s)
+    pop, st = m.calc_molecular_populations(start_mode=abi.RT_START_CHAINED)
+    m.close()
+    for q, (lo, hi) in zip((a, a.sliced(1, 3)), ranges):
+        m1 = solver_mod.Model(q)
+        pop1, st1 = m1.calc_molecular_populations(start_mode=abi.RT_START_CHAINED)
+        m1.close()
+        assert np.array_equal(pop[lo:hi], pop1) and np.array_equal(st["iters"][lo:hi], st1["iters"])
+
+
+def test_handle_survives_recoverable_errors(solver_mod, problems):
+    """A recoverable error must not poison the handle: error -> rt_cloud_upload -> solve on the SAME rt_model (the
+    reuse-one-model sweep pattern of bench.py / SweepQueue)."""
+    from radiative_transfer_b200 import abi
+    p = problems("generic", 3)
+    m = solver_mod.Model(p)
+    ref_pop, ref_st = m.calculate_populations()
+    q = copy.copy(p)
+    s, hold = q.layer_soa()
+    s.dust_ncomp = 2
+    assert m.L_.rt_cloud_upload(m.h, C.byref(s)) == 4            # RT_ERR_DUST_INCONSISTENT, resident cloud untouched
+    with pytest.raises(solver_mod.RtError, match="chained"):
+        m.solve_device(start_mode=abi.RT_START_CHAINED)           # RT_ERR_INVALID
+    b = m.boundary_layer_populations()
+    with pytest.raises(solver_mod.RtError, match="up > low"):
+        m.lim_luminosity(b, [3], [5])
+    m.cloud_upload(p)                                             # must succeed on the same handle
+    pop, st = m.calculate_populations()
+    assert np.array_equal(pop, ref_pop) and np.array_equal(st["iters"], ref_st["iters"])
+    bad = copy.copy(p)
+    bad.model_first = np.array([0, 2, 2, 3], dtype=np.int32)      # not strictly ascending
+    with pytest.raises(solver_mod.RtError, match="model_first"):
+        m.cloud_upload(bad)
+    m.cloud_upload(p)
+    pop, st = m.calculate_populations()
+    assert np.array_equal(pop, ref_pop)
+    m.close()
+
+
 # ---- BASELINE.json full sizes: size-independent properties -------------------------------------------------------
 def test_full_size_ch3oh_properties(solver_mod, best_checker):
     """Config 2 (CH3OH-A, N = 768, L = 200): normalisation, fixed-point property, layer independence, and parity

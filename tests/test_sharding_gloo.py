@@ -16,7 +16,7 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, L, q):
+def _worker(rank, world, port, L, q, cyclic=False):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     sys.path.insert(0, root)
@@ -32,21 +32,21 @@ def _worker(rank, world, port, L, q):
     def solve_fn(sub):
         pop, st, _ = chk.solve(sub)
         return pop, st
-    pop, st = sharding.solve_sharded(p, solve_fn, world, rank)
+    pop, st = sharding.solve_sharded(p, solve_fn, world, rank, cyclic=cyclic)
     if rank == 0:
         q.put((pop, st["iters"].copy(), st["converged"].copy()))
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("L", [5, 2])
-def test_sharded_equals_unsharded(L, port):
+@pytest.mark.parametrize("L,cyclic", [(5, False), (2, False), (5, True), (1, True)])
+def test_sharded_equals_unsharded(L, cyclic, port):
     import torch.multiprocessing as mp
     from radiative_transfer_b200 import synthetic
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     world, tcp = 2, _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, tcp, L, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, tcp, L, q, cyclic)) for r in range(world)]
     for pr in procs:
         pr.start()
     pop, iters, conv = q.get(timeout=180)
@@ -70,6 +70,12 @@ def test_layer_range_and_sweep_assign():
             assert max(sizes) - min(sizes) <= 1
     pts = sorted(sum((sharding.sweep_assign(512, 8, k) for k in range(8)), []))
     assert pts == list(range(512))
+    for L in (1, 7, 400):
+        for w in (1, 3, 8):
+            for cyc in (False, True):
+                got = np.sort(np.concatenate([sharding.layer_indices(L, w, k, cyc) for k in range(w)]))
+                assert np.array_equal(got, np.arange(L))
+    assert sharding.layer_indices(10, 4, 1, True).tolist() == [1, 5, 9]
 
 
 def _queue_worker(rank, world, port, n, q):
@@ -85,7 +91,9 @@ def _queue_worker(rank, world, port, n, q):
     for i in sharding.SweepQueue(n):
         mine.append(i)
         time.sleep(0.002 * (1 + 3 * rank))  # rank 1 is the slow one: it must end up with fewer points
-    q.put((rank, mine))
+    # a SECOND sweep in the same process group starts from zero again (own counter per sweep)
+    second = [i for i in sharding.SweepQueue(n // 2)]
+    q.put((rank, mine, second))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -99,17 +107,21 @@ def test_sweep_queue_hands_every_point_out_once():
     procs = [ctx.Process(target=_queue_worker, args=(r, world, tcp, n, q)) for r in range(world)]
     for pr in procs:
         pr.start()
-    got = dict(q.get(timeout=120) for _ in range(world))
+    res = [q.get(timeout=120) for _ in range(world)]
+    got = {r: a for r, a, b in res}
+    second = {r: b for r, a, b in res}
     for pr in procs:
         pr.join(timeout=60)
         assert pr.exitcode == 0
     assert sorted(got[0] + got[1]) == list(range(n))
     assert len(got[0]) > len(got[1]) > 0
+    assert sorted(second[0] + second[1]) == list(range(n // 2))
 
 
 def test_sweep_queue_single_process_and_stack_clouds():
     from radiative_transfer_b200 import sharding, synthetic
     assert list(sharding.SweepQueue(5)) == [0, 1, 2, 3, 4]
+    assert list(sharding.SweepQueue(3)) == [0, 1, 2]
     a = synthetic.small("ch3oh_small", L=3)
     b = synthetic.config_ch3oh(L=2, n_vt=2, n_k=6, n_j=8, cloud_kw=dict(t_hi=200.0))
     s, ranges = sharding.stack_clouds([a, b])
