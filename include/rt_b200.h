@@ -243,6 +243,9 @@ rt_status rt_solve_device(rt_model* m, int start_mode, int max_iter, double min_
 rt_status rt_get_status(rt_model* m, rt_layer_status* st);
 rt_status rt_get_populations(rt_model* m, double* pop);
 rt_status rt_set_populations(rt_model* m, const double* pop);
+/* Populations [L*N] copied device-to-device into a caller-owned DEVICE buffer on the model's GPU (the sharded solve hands
+ * them to the NCCL all_gather without a host round trip).  Synchronous: complete on return. */
+rt_status rt_copy_populations_device(rt_model* m, double* dst_device);
 
 /* Instrumentation for bench.py / profiles: kernel launch count and CUDA-event time (ms) per kernel class since
  * the last reset.  names/ms/launches arrays of capacity `cap`; returns number of classes through *n. */

@@ -574,7 +574,7 @@ int ref_solve(const rt_model_desc* d, const rt_layer_soa* lay, double* pop, int 
     null_buf nb;
     cout_redirect quiet(&nb);
     const std::string name = c->diagram->mol.name;
-    const double t0 = omp_get_wtime();
+    double t0 = 0.;
 #pragma omp parallel num_threads(nthreads)
     {
         iteration_scheme_lvg* s;
@@ -582,6 +582,11 @@ int ref_solve(const rt_model_desc* d, const rt_layer_soa* lay, double* pop, int 
         s = make_scheme(c);
         counting_scheme cs{s, 0};
         iteration_control<counting_scheme> ctl(&cs);
+        // the clock starts when every thread has its private scheme object (the reference builds those once per model,
+        // radiative_transfer.cpp:152-201; their serialised construction is set-up, not the solve being timed)
+#pragma omp barrier
+#pragma omp master
+        t0 = omp_get_wtime();
 #pragma omp for schedule(dynamic, 1)
         for (int l = lay_begin; l < lay_end; l++) {
             const cloud_layer cl = c->cloud->lay_array[l];

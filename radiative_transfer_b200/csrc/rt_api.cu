@@ -756,6 +756,15 @@ rt_status rt_get_populations(rt_model* m, double* pop)
     return RT_OK;
 }
 
+rt_status rt_copy_populations_device(rt_model* m, double* dst_device)
+{
+    NEED_CLOUD();
+    if (!dst_device) return RT_ERR_INVALID;
+    CK(cudaMemcpyAsync(dst_device, m->d.pop, sizeof(double) * (size_t)m->d.L * m->d.N, cudaMemcpyDeviceToDevice, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    return RT_OK;
+}
+
 rt_status rt_get_status(rt_model* m, rt_layer_status* st)
 {
     NEED_CLOUD();

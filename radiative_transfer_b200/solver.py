@@ -26,7 +26,7 @@ ENTRY_POINTS = [
     "rt_calc_molecular_populations", "rt_solve_device", "rt_get_status", "rt_get_populations", "rt_set_populations",
     "rt_profile_reset", "rt_profile_get", "rt_iterations_enqueued", "rt_maser_postpass", "rt_cloud_rebuild",
     "rt_profile_get_work", "rt_launch_count", "rt_timer_begin", "rt_timer_end", "rt_device_fp64_peak",
-    "rt_lim_luminosity", "rt_set_gain_width_line",
+    "rt_lim_luminosity", "rt_set_gain_width_line", "rt_copy_populations_device",
 ]
 
 
@@ -168,6 +168,10 @@ class Model:
         pop = np.zeros((self.L, self.N))
         self._ck(self.L_.rt_get_populations(self.h, abi.dptr(pop)), "rt_get_populations")
         return pop
+
+    def copy_populations_device(self, dst_ptr: int):
+        """Populations [L, N] device-to-device into a caller-owned CUDA buffer (e.g. a torch tensor's data_ptr())."""
+        self._ck(self.L_.rt_copy_populations_device(self.h, C.c_void_p(int(dst_ptr))), "rt_copy_populations_device")
 
     def set_populations(self, pop):
         pop = np.ascontiguousarray(pop, dtype=np.float64)
