@@ -60,6 +60,11 @@ class Checker:
         s, h2 = p.layer_soa()
         return d, s, (h1, h2)
 
+    def set_lu_variant(self, v: int):
+        """Rounding-sensitivity probe of the restated lu_matrix_solve (oracle/shim/linear_algebra.h; ref only); 0 = off."""
+        assert self.kind == "ref"
+        self.lib.ref_set_lu_variant(int(v))
+
     def lu_solve(self, a, b):
         a = np.array(a, dtype=np.float64, order="C"); b = np.array(b, dtype=np.float64)
         self._f("lu_solve")(self.abi.dptr(a), self.abi.dptr(b), C.c_int(b.shape[0]))

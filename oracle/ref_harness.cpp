@@ -392,6 +392,8 @@ ref_ctx* build_ctx(const rt_model_desc* d, const rt_layer_soa* lay)
 extern "C" {
 
 int ref_abi_version(void) { return 1; }
+// rounding-sensitivity probe of the restated lu_matrix_solve (oracle/shim/linear_algebra.h); 0 = the textbook solve
+void ref_set_lu_variant(int v) { shim_lu_variant() = v; }
 
 // the restated dense solver itself (oracle/shim/linear_algebra.h), for LU unit tests: a is [n][n] row-major
 int ref_lu_solve(double* a, double* b, int n)
