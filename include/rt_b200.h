@@ -225,6 +225,17 @@ rt_status rt_assemble(rt_model* m, const double* pop, double* matrix, double* df
  * the single-line overload :503-526).  pop HOST [N] for that layer. */
 rt_status rt_intensity(rt_model* m, int lay, int up, int low, const double* pop, double* intensity);
 
+/* rt_intensity without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and result as rt_intensity; the device copies of `pop` and of the result block live in a file-scope
+ * device array of RT_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit, so nb_lev is limited to
+ * RT_NOALLOC_MAX_LEVELS (RT_ERR_UNSUPPORTED beyond, message in rt_last_error).  Calls no cudaMalloc / cudaFree /
+ * allocating routine.  All calls on one GPU share the array: calls that overlap on the GPU (other host threads, other
+ * rt_model handles on the same device) race -- serialise them.  The call itself is synchronous. */
+#define RT_NOALLOC_MAX_LEVELS 1024
+#define RT_NOALLOC_SCRATCH_BYTES ((RT_NOALLOC_MAX_LEVELS + 16) * 8)
+rt_status rt_intensity_noalloc(rt_model* m, int lay, int up, int low, const double* pop, double* intensity);
+
 /* == iteration_control::calculate_populations for every layer (iteration_control.h:196-242), all layers at
  * once on the device.  pop HOST [L*N] in/out (input used when start_mode == RT_START_GIVEN). */
 rt_status rt_solve(rt_model* m, double* pop, int start_mode, int max_iter, double min_err, int accel,

@@ -27,6 +27,7 @@ ENTRY_POINTS = [
     "rt_profile_reset", "rt_profile_get", "rt_iterations_enqueued", "rt_maser_postpass", "rt_cloud_rebuild",
     "rt_profile_get_work", "rt_launch_count", "rt_timer_begin", "rt_timer_end", "rt_device_fp64_peak",
     "rt_lim_luminosity", "rt_set_gain_width_line", "rt_copy_populations_device",
+    "rt_intensity_noalloc",
 ]
 
 
@@ -123,6 +124,13 @@ class Model:
         pop = np.ascontiguousarray(pop, dtype=np.float64)
         out = C.c_double()
         self._ck(self.L_.rt_intensity(self.h, int(lay), int(up), int(low), abi.dptr(pop), C.byref(out)), "rt_intensity")
+        return out.value
+
+    def intensity_calc_noalloc(self, lay, up, low, pop):
+        """rt_intensity_noalloc: intensity_calc through the fixed device scratch array (no allocation; N <= 1024)."""
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        out = C.c_double()
+        self._ck(self.L_.rt_intensity_noalloc(self.h, int(lay), int(up), int(low), abi.dptr(pop), C.byref(out)), "rt_intensity_noalloc")
         return out.value
 
     # -- iteration_control::calculate_populations (iteration_control.h:196-242), every layer ------------------

@@ -5,7 +5,7 @@ set -e
 cd "$(dirname "$0")/.."
 name=$1; shift
 mkdir -p variants/obj_$name
-for f in rt_api coupling_kernels lu_kernels controller_kernels misc_kernels fused_kernels; do
+for f in rt_api coupling_kernels lu_kernels controller_kernels misc_kernels fused_kernels noalloc_api; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC "$@" \
     -c radiative_transfer_b200/csrc/$f.cu -o variants/obj_$name/$f.o &
 done
