@@ -1,5 +1,6 @@
 // fused_kernels.cu -- the whole iteration of one layer in ONE persistent CTA, for molecules whose rate matrix fits in
-// shared memory (Np <= 160: OH hyperfine N = 56, NH3/H2CO, H2O N = 150).
+// shared memory (OH hyperfine N = 56, NH3, H2CO: register-resident LU; up to N ~ 158, e.g. H2O at the N = 150 the reference
+// driver uses: the UNPADDED N x (N + 1) matrix fills the CTA's shared memory and the molecule constants stay in L2).
 //
 // Configs 1 and 3 of BASELINE.json (OH, N = 56, un-accelerated, up to 15000 iterations per layer) are launch-latency
 // problems for the multi-kernel path: a step is ~10 launches of a few microseconds of work each.  Here one CTA per
@@ -30,11 +31,18 @@ __host__ __device__ inline size_t fused_const_doubles(const DevModel& d)
     const size_t halves = d.scheme == RT_SCHEME_LINE_OVERLAP ? 6 * G : 0;
     return 3 * R + R * (d.ncomp > 0 ? d.ncomp : 1) + G + axes + halves + (ints + 1) / 2 + 2;
 }
-__host__ __device__ inline size_t fused_smem_doubles(const DevModel& d)
+// Dimension of the matrix the CTA factors.  The register-resident LU (Np <= 96) works on whole 32-row slots like the
+// blocked multi-kernel LU; above that the matrix is NOT padded to a multiple of 32 (N = 150: 181 KB instead of 206 KB, the
+// difference between fitting and not fitting): N, rounded up to an even number so that the row stride N + 1 stays odd
+// (conflict-free column walks); an odd N gets one identity row / column, which is what Cmat holds there anyway.
+__host__ __device__ inline int fused_dim(const DevModel& d) { return d.Np <= 96 ? d.Np : ((d.N + 1) & ~1); }
+// cs: molecule constants staged in shared memory (small molecules); otherwise read through L1/L2 every iteration
+__host__ __device__ inline size_t fused_smem_doubles(const DevModel& d, bool cs)
 {
-    const size_t Np = d.Np, R = d.R > 0 ? d.R : 1;
-    return Np * (Np + 1) + Np + 2 * R + 64 + (fused_c_in_smem(d.Np) ? Np * (Np + 1) : 0) + fused_const_doubles(d);
+    const size_t Nm = fused_dim(d), R = d.R > 0 ? d.R : 1;
+    return Nm * (Nm + 1) + Nm + 2 * R + 64 + (fused_c_in_smem(d.Np) ? Nm * (Nm + 1) : 0) + (cs ? fused_const_doubles(d) : 0);
 }
+static bool fused_fits(const DevModel& d, bool cs);
 
 // Arg-max of the 64-bit keys of warp 0 (two REDUX), interchange of positions k <-> p in s_row, publication of the pivot's
 // physical row, the displaced row, p and 1/pivot for parity k & 1.  key = |a| bits with the low byte replaced by
@@ -87,6 +95,38 @@ __device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int Np
     }
 #pragma unroll
     for (int q = 0; q < NQ; q++) gnew[lane + 32 * q] = b[q];
+}
+
+// the same for a dimension n that is not a multiple of 32 (n <= 32 NQ): lanes beyond n idle along
+template <int NQ>
+__device__ __forceinline__ void fused_backsolve_n(const double* M, int ldm, int n, const short* rowf, double* gnew, int lane)
+{
+    double b[NQ], rd[NQ];
+    const double* rowp[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; q++) {
+        const int r = lane + 32 * q;
+        const bool ok = r < n;
+        rowp[q] = M + (size_t)rowf[ok ? r : 0] * ldm;
+        b[q] = ok ? rowp[q][n] : 0.;
+        rd[q] = ok ? __drcp_rn(rowp[q][r]) : 0.;
+    }
+#pragma unroll
+    for (int qi = NQ - 1; qi >= 0; qi--) {
+#pragma unroll 8
+        for (int ii = 31; ii >= 0; ii--) {
+            const int i = 32 * qi + ii;
+            if (i >= n) continue; // uniform
+            const double xi = __shfl_sync(0xffffffffu, b[qi] * rd[qi], ii);
+#pragma unroll
+            for (int q = 0; q < qi; q++) b[q] -= rowp[q][i] * xi;
+            if (lane < ii) b[qi] -= rowp[qi][i] * xi;
+            else if (lane == ii) b[qi] = xi;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < NQ; q++)
+        if (lane + 32 * q < n) gnew[lane + 32 * q] = b[q];
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -285,14 +325,16 @@ __device__ __forceinline__ void fused_lu_regs(double* M, int ldm, short* s_row, 
 
 // LUV: 1..3 = register-resident LU with NQ = LUV (Np = 32 LUV), 0 = LU in shared memory (any Np <= 160).  One kernel per
 // variant so that the register allocation of the small, common sizes (two CTAs per SM) is not set by the large ones.
-template <int LUV>
+// CS: molecule constants staged in shared memory (false: the matrix needs the room; they are read through L1/L2).
+template <int LUV, bool CS = true>
 __global__ void __launch_bounds__(FUSED_THREADS, (LUV == 1 || LUV == 2) ? 2 : 1)
 k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
 {
     const int a = blockIdx.x;
     if (a >= nlay || a >= *d.n_active) return;
     const int lay = d.active[a];
-    const int N = d.N, Np = d.Np, ldm = Np + 1, R = d.R;
+    // Np: dimension of the matrix in shared memory (fused_dim); NpG: padded dimension of the global arrays (Cmat, rhs)
+    const int N = d.N, Np = fused_dim(d), NpG = d.Np, ldm = Np + 1, R = d.R;
     extern __shared__ __align__(16) double sm[];
     double* M = sm;                      // [Np][ldm]
     double* s_pop = M + (size_t)Np * ldm; // [Np]
@@ -305,8 +347,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     __shared__ double s_eq[FUSED_THREADS / 32];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // the collisional matrix of the layer is constant over the iteration: staged in shared memory when it fits
-    const double* C = d.Cmat + (size_t)lay * Np * Np;
-    int ldc = Np;
+    const double* C = d.Cmat + (size_t)lay * NpG * NpG;
+    int ldc = NpG;
     double* arena = s_yu + (R > 0 ? R : 1);
     if (fused_c_in_smem(Np)) {
         double* s_C = arena;
@@ -315,16 +357,20 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         C = s_C;
         arena += (size_t)Np * ldc;
     }
-    // molecule constants -> shared memory (fused_const_doubles)
+    // molecule constants: staged in shared memory (CS, fused_const_doubles) or read in place through L1/L2
     const int Rn = R > 0 ? R : 1, Gn = d.G > 0 ? d.G : 1, nc = d.ncomp > 0 ? d.ncomp : 1, nnz = d.row_ptr[N];
-    double* c_Aul = arena; double* c_Alu = c_Aul + Rn; double* c_E = c_Alu + Rn; double* c_sig = c_E + Rn;
-    double* c_dxn = c_sig + (size_t)Rn * nc;
-    // axes of the escape-probability tables (binary searches every iteration), halves of the pair evaluations
+    const double *c_Aul = d.tr_Aul, *c_Alu = d.tr_Alu, *c_E = d.tr_E, *c_sig = d.tr_sigma, *c_dxn = d.grp_dxn;
+    const int *c_grp = d.grp, *c_tru = d.tr_u, *c_trl = d.tr_l, *c_rptr = d.row_ptr, *c_rcol = d.row_col, *c_rline = d.row_line;
+    const int* c_task = nullptr; // [2G] group * 2 + half; without staging (LVG scheme only) task t is line t
+    double* c_half = nullptr;    // [2G][3] halves of the pair evaluations (overlap scheme)
     DevLvg lvg = d.lvg;
     DevOverlap ov0 = d.ov[0], ov1 = d.ov[1];
-    double* c_ax = c_dxn + Gn;
-    {
-        double* a = c_ax;
+    __shared__ int s_ntask;
+    if constexpr (CS) {
+        double* w_Aul = arena; double* w_Alu = w_Aul + Rn; double* w_E = w_Alu + Rn; double* w_sig = w_E + Rn;
+        double* w_dxn = w_sig + (size_t)Rn * nc;
+        // axes of the escape-probability tables (binary searches every iteration)
+        double* a = w_dxn + Gn;
         for (int e = tid; e < lvg.nb_d; e += FUSED_THREADS) a[e] = d.lvg.delta[e];
         lvg.delta = a; a += lvg.nb_d;
         for (int e = tid; e < lvg.nb_g; e += FUSED_THREADS) a[e] = d.lvg.gamma[e];
@@ -344,40 +390,41 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
                 o.gamma = a; a += o.nb_g;
             }
         }
-        c_ax = a;
-    }
-    double* c_half = c_ax; // [2G][3]
-    int* c_grp = (int*)(c_half + (d.scheme == RT_SCHEME_LINE_OVERLAP ? 6 * Gn : 0)); int* c_tru = c_grp + 3 * Gn; int* c_trl = c_tru + Rn; int* c_rptr = c_trl + Rn;
-    int* c_rcol = c_rptr + N + 1; int* c_rline = c_rcol + 2 * Rn; int* c_task = c_rline + 2 * Rn; // [2G] group * 2 + half
-    __shared__ int s_ntask;
-    for (int e = tid; e < R; e += FUSED_THREADS) {
-        c_Aul[e] = d.tr_Aul[e]; c_Alu[e] = d.tr_Alu[e]; c_E[e] = d.tr_E[e]; c_tru[e] = d.tr_u[e]; c_trl[e] = d.tr_l[e];
-        for (int k = 0; k < d.ncomp; k++) c_sig[(size_t)e * d.ncomp + k] = d.tr_sigma[(size_t)e * d.ncomp + k];
-    }
-    for (int e = tid; e < d.G; e += FUSED_THREADS) {
-        c_dxn[e] = d.grp_dxn[e];
-        c_grp[3 * e] = d.grp[3 * e]; c_grp[3 * e + 1] = d.grp[3 * e + 1]; c_grp[3 * e + 2] = d.grp[3 * e + 2];
-    }
-    if (d.scheme != RT_SCHEME_LINE_OVERLAP) { // one task per line
-        for (int g = tid; g < d.G; g += FUSED_THREADS) c_task[g] = 2 * g;
-        if (tid == 0) s_ntask = d.G;
-    }
-    else {
-        __syncthreads();
-        if (tid == 0) { // one task per single line, two per overlapping pair
-            int nt = 0;
-            for (int g = 0; g < d.G; g++) {
-                c_task[nt++] = 2 * g;
-                if (c_grp[3 * g] == 2) c_task[nt++] = 2 * g + 1;
-            }
-            s_ntask = nt;
+        c_half = a;
+        int* w_grp = (int*)(c_half + (d.scheme == RT_SCHEME_LINE_OVERLAP ? 6 * Gn : 0)); int* w_tru = w_grp + 3 * Gn; int* w_trl = w_tru + Rn;
+        int* w_rptr = w_trl + Rn; int* w_rcol = w_rptr + N + 1; int* w_rline = w_rcol + 2 * Rn; int* w_task = w_rline + 2 * Rn;
+        for (int e = tid; e < R; e += FUSED_THREADS) {
+            w_Aul[e] = d.tr_Aul[e]; w_Alu[e] = d.tr_Alu[e]; w_E[e] = d.tr_E[e]; w_tru[e] = d.tr_u[e]; w_trl[e] = d.tr_l[e];
+            for (int k = 0; k < d.ncomp; k++) w_sig[(size_t)e * d.ncomp + k] = d.tr_sigma[(size_t)e * d.ncomp + k];
         }
+        for (int e = tid; e < d.G; e += FUSED_THREADS) {
+            w_dxn[e] = d.grp_dxn[e];
+            w_grp[3 * e] = d.grp[3 * e]; w_grp[3 * e + 1] = d.grp[3 * e + 1]; w_grp[3 * e + 2] = d.grp[3 * e + 2];
+        }
+        if (d.scheme != RT_SCHEME_LINE_OVERLAP) { // one task per line
+            for (int g = tid; g < d.G; g += FUSED_THREADS) w_task[g] = 2 * g;
+            if (tid == 0) s_ntask = d.G;
+        }
+        else {
+            __syncthreads();
+            if (tid == 0) { // one task per single line, two per overlapping pair
+                int nt = 0;
+                for (int g = 0; g < d.G; g++) {
+                    w_task[nt++] = 2 * g;
+                    if (w_grp[3 * g] == 2) w_task[nt++] = 2 * g + 1;
+                }
+                s_ntask = nt;
+            }
+        }
+        for (int e = tid; e <= N; e += FUSED_THREADS) w_rptr[e] = d.row_ptr[e];
+        for (int e = tid; e < nnz; e += FUSED_THREADS) { w_rcol[e] = d.row_col[e]; w_rline[e] = d.row_line[e]; }
+        c_Aul = w_Aul; c_Alu = w_Alu; c_E = w_E; c_sig = w_sig; c_dxn = w_dxn;
+        c_grp = w_grp; c_tru = w_tru; c_trl = w_trl; c_rptr = w_rptr; c_rcol = w_rcol; c_rline = w_rline; c_task = w_task;
     }
+    else if (tid == 0) s_ntask = d.G; // LVG scheme only (fused_supported): one task per line
     const bool same_axes = d.ov_same_axes != 0;
-    for (int e = tid; e <= N; e += FUSED_THREADS) c_rptr[e] = d.row_ptr[e];
-    for (int e = tid; e < nnz; e += FUSED_THREADS) { c_rcol[e] = d.row_col[e]; c_rline[e] = d.row_line[e]; }
     double* gpop = d.pop + (size_t)lay * N;
-    double* gnew = d.rhs + (size_t)lay * Np;
+    double* gnew = d.rhs + (size_t)lay * NpG;
     const LayerCtx ctx = dev_layer_ctx(d, lay);
 
     for (;;) {
@@ -387,7 +434,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         // ---- K1a: mean intensities -> radiative rates (iteration_lvg.cpp:163-185, :428-501) ------------------------
         const int ntask = s_ntask;
         for (int t = tid; t < ntask; t += FUSED_THREADS) {
-            const int gi = c_task[t] >> 1, half = c_task[t] & 1;
+            const int task = CS ? c_task[t] : 2 * t;
+            const int gi = task >> 1, half = task & 1;
             const int nb = c_grp[3 * gi], la = c_grp[3 * gi + 1];
             const int u1 = c_tru[la], l1 = c_trl[la];
             const double A1ul = c_Aul[la], A1lu = c_Alu[la];
@@ -528,8 +576,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         }
         if (warp == 0) {
             if constexpr (LUV > 0) fused_backsolve<LUV>(M, ldm, Np, s_row, gnew, lane);
-            else if (Np == 128) fused_backsolve<4>(M, ldm, Np, s_row, gnew, lane);
-            else fused_backsolve<5>(M, ldm, Np, s_row, gnew, lane);
+            else if (Np <= 128) fused_backsolve_n<4>(M, ldm, Np, s_row, gnew, lane);
+            else fused_backsolve_n<5>(M, ldm, Np, s_row, gnew, lane);
         }
         __syncthreads();
         // ---- K3: controller step (iteration_control.h:84-137), shared with the multi-kernel path --------------------
@@ -538,33 +586,44 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     }
 }
 
+static bool fused_fits(const DevModel& d, bool cs) { return fused_smem_doubles(d, cs) * sizeof(double) <= FUSED_DYN_SMEM_MAX; }
+
 void launch_fused_solve(const DevModel& d, cudaStream_t s, int nlay, int accel, int max_iter, double min_err)
 {
     g_rt_launches++;
-    const size_t smem = fused_smem_doubles(d) * sizeof(double);
+    const bool cs = fused_fits(d, true);
+    const size_t smem = fused_smem_doubles(d, cs) * sizeof(double);
     switch (d.Np) {
     case 32: k_fused_solve<1><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
     case 64: k_fused_solve<2><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
     case 96: k_fused_solve<3><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
-    default: k_fused_solve<0><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+    default:
+        if (cs) k_fused_solve<0, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        else k_fused_solve<0, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
     }
 }
 
+// One CTA per layer with the whole matrix in shared memory: every size whose UNPADDED matrix fits (N up to ~158 for a
+// molecule with ~700 lines).  Without room for the staged constants only the LVG scheme is supported (the overlap scheme's
+// pair halves live in that staging area; its molecules are small anyway).
 bool fused_supported(const DevModel& d)
 {
-    return d.Np <= 160 && fused_smem_doubles(d) * sizeof(double) <= FUSED_DYN_SMEM_MAX;
+    if (fused_dim(d) > 160) return false;
+    if (d.Np <= 96) return fused_fits(d, true);
+    return fused_fits(d, true) || (d.scheme != RT_SCHEME_LINE_OVERLAP && fused_fits(d, false));
 }
 
-template <int LUV> static cudaError_t fused_set_smem()
+template <int LUV, bool CS> static cudaError_t fused_set_smem()
 {
-    return cudaFuncSetAttribute(k_fused_solve<LUV>, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_DYN_SMEM_MAX);
+    return cudaFuncSetAttribute(k_fused_solve<LUV, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_DYN_SMEM_MAX);
 }
 
 cudaError_t fused_kernels_init()
 {
-    cudaError_t e = fused_set_smem<0>();
-    if (e == cudaSuccess) e = fused_set_smem<1>();
-    if (e == cudaSuccess) e = fused_set_smem<2>();
-    if (e == cudaSuccess) e = fused_set_smem<3>();
+    cudaError_t e = fused_set_smem<0, true>();
+    if (e == cudaSuccess) e = fused_set_smem<0, false>();
+    if (e == cudaSuccess) e = fused_set_smem<1, true>();
+    if (e == cudaSuccess) e = fused_set_smem<2, true>();
+    if (e == cudaSuccess) e = fused_set_smem<3, true>();
     return e;
 }

@@ -401,6 +401,8 @@ def small(name: str, L: int = 6) -> Problem:
         return config_ch3oh(L=L, n_vt=3, n_k=8, n_j=10)  # N = 240
     if name == "h2o_small":
         return config_h2o(L=L, N=150, cloud_kw=H2O_THICK_CLOUD)
+    if name == "h2o_odd":
+        return config_h2o(L=L, N=131)  # odd level count between the register-resident and the blocked LU sizes
     if name == "nh3":
         return config_nh3(L=L)
     if name == "h2co":
