@@ -77,13 +77,18 @@ typedef struct rt_params {
 } rt_params;
 
 /* One collision_data table (coll_rates.h:12-41).  coeff is [imax][jmax] row-major, imax = nb_lev*(nb_lev-1)/2,
- * row index i*(i-1)/2 + j for the transition i -> j (i > j).  The library derives coeff_deriv with the linear
- * rule of collision_data::calc_coeff_deriv (coll_rates.cpp:61-69). */
+ * row index i*(i-1)/2 + j for the transition i -> j (i > j).  The library derives coeff_deriv itself:
+ * RT_INTERP_LINEAR        collision_data: first differences (calc_coeff_deriv, coll_rates.cpp:61-69), linear get_rate (:54-59);
+ * RT_INTERP_CUBIC_SPLINE  collision_data_cub_spline (coll_rates.h:44-53): natural-spline second derivatives
+ *                         (calc_coeff_deriv, coll_rates.cpp:89-119) and the cubic get_rate with its fabs (:121-132).  ABI 5. */
+enum { RT_INTERP_LINEAR = 0, RT_INTERP_CUBIC_SPLINE = 1 };
 typedef struct rt_coll_table {
     int nb_lev;
     int jmax;
     const double* tgrid; /* [jmax] ascending */
     const double* coeff; /* [imax][jmax]     */
+    int interp;          /* RT_INTERP_* */
+    int reserved0;
 } rt_coll_table;
 
 /* One dust_component as seen by dust_component::absorption (dust_model.cpp:473-490). */

@@ -142,6 +142,9 @@ inline void flatten_model(const iteration_scheme_lvg* scheme, const energy_diagr
         for (int i = 0; i < t->imax; i++) memcpy(&f.coeff[k][(size_t)i * t->jmax], t->coeff[i], sizeof(double) * t->jmax);
         f.tables[k].nb_lev = t->nb_lev; f.tables[k].jmax = t->jmax;
         f.tables[k].tgrid = f.tgrid[k].data(); f.tables[k].coeff = f.coeff[k].data();
+        // a table object of the cubic-spline class (coll_rates.h:44-53) is evaluated with its own rule on the GPU
+        f.tables[k].interp = dynamic_cast<const collision_data_cub_spline*>(t) ? RT_INTERP_CUBIC_SPLINE : RT_INTERP_LINEAR;
+        f.tables[k].reserved0 = 0;
     }
     d.nb_neutral_tables = nb1; d.nb_electron_tables = nb2 - nb1; d.tables = f.tables.data();
 

@@ -90,8 +90,10 @@ struct synth_einstein : public einstein_coeff {
     }
 };
 
-struct synth_coll_data : public collision_data {
-    synth_coll_data(const rt_coll_table* t)
+// fills the members of either table class of the reference and runs ITS calc_coeff_deriv (virtual)
+template <class Base> struct synth_coll_data_t : public Base {
+    using Base::nb_lev; using Base::jmax; using Base::imax; using Base::tgrid; using Base::coeff; using Base::coeff_deriv;
+    synth_coll_data_t(const rt_coll_table* t)
     {
         nb_lev = t->nb_lev;
         jmax = t->jmax;
@@ -102,9 +104,16 @@ struct synth_coll_data : public collision_data {
         memcpy(*coeff, t->coeff, sizeof(double) * (size_t)imax * jmax);
         coeff_deriv = alloc_2d_array<double>(imax, jmax);
         memset(*coeff_deriv, 0, sizeof(double) * (size_t)imax * jmax);
-        calc_coeff_deriv(); // the reference's own linear-derivative rule, coll_rates.cpp:61-69
+        Base::calc_coeff_deriv(); // the reference's own rule: linear coll_rates.cpp:61-69, cubic spline :89-119
     }
 };
+typedef synth_coll_data_t<collision_data> synth_coll_data;
+typedef synth_coll_data_t<collision_data_cub_spline> synth_coll_data_spline;
+static collision_data* make_coll_data(const rt_coll_table* t)
+{
+    if (t->interp == RT_INTERP_CUBIC_SPLINE) return new synth_coll_data_spline(t);
+    return new synth_coll_data(t);
+}
 
 // A collisional_transitions whose tables are synthetic but whose MIXING RULES are the reference's own compiled
 // member functions.  ch3oh_collisions / oh_hf_collisions / h2o_collisions add no data members and their
@@ -118,7 +127,7 @@ struct synth_collisions : public collisional_transitions {
         nb1 = d->nb_neutral_tables;
         nb2 = nb1 + d->nb_electron_tables;
         nb3 = nb2;
-        for (int k = 0; k < nb3; k++) coll_data.push_back(new synth_coll_data(&d->tables[k]));
+        for (int k = 0; k < nb3; k++) coll_data.push_back(make_coll_data(&d->tables[k]));
         max_temp = new double[nb3 > 0 ? nb3 : 1];
         for (int k = 0; k < nb3; k++) max_temp[k] = coll_data[k]->get_max_temp();
     }

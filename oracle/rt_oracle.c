@@ -89,10 +89,10 @@ static void lu_solve(double* a, double* b, int n)
 /* model context                                                                                           */
 /* ------------------------------------------------------------------------------------------------------- */
 typedef struct ora_table {
-    int nb_lev, jmax, imax;
+    int nb_lev, jmax, imax, interp;
     const double* tgrid;
     const double* coeff;
-    double* deriv; /* [imax][jmax], collision_data::calc_coeff_deriv, coll_rates.cpp:61-69 */
+    double* deriv; /* [imax][jmax], collision_data::calc_coeff_deriv, coll_rates.cpp:61-69; cubic spline (:89-119): second derivatives */
     double max_temp;
 } ora_table;
 
@@ -147,10 +147,32 @@ static ora_model* model_create(const rt_model_desc* d)
         t->tgrid = s->tgrid; t->coeff = s->coeff;
         t->max_temp = s->tgrid[s->jmax - 1]; /* get_max_temp, coll_rates.h:23 */
         t->deriv = (double*)calloc((size_t)t->imax * t->jmax + 1, sizeof(double));
-        for (int i = 0; i < t->imax; i++)
-            for (int j = 0; j < t->jmax - 1; j++)
-                t->deriv[(size_t)i * t->jmax + j] = (s->coeff[(size_t)i * t->jmax + j + 1] - s->coeff[(size_t)i * t->jmax + j])
-                                                    / (s->tgrid[j + 1] - s->tgrid[j]);
+        t->interp = s->interp;
+        if (s->interp == RT_INTERP_CUBIC_SPLINE) {
+            /* collision_data_cub_spline::calc_coeff_deriv, coll_rates.cpp:89-119 */
+            double* u = (double*)calloc(t->jmax, sizeof(double));
+            const double* tg = s->tgrid;
+            for (int i = 0; i < t->imax; i++) {
+                const double* c = s->coeff + (size_t)i * t->jmax;
+                double* d2 = t->deriv + (size_t)i * t->jmax;
+                d2[0] = u[0] = 0.;
+                for (int j = 1; j < t->jmax - 1; j++) {
+                    const double sig = (tg[j] - tg[j - 1]) / (tg[j + 1] - tg[j - 1]);
+                    const double p = sig * d2[j - 1] + 2.;
+                    d2[j] = (sig - 1.) / p;
+                    u[j] = (c[j + 1] - c[j]) / (tg[j + 1] - tg[j]) - (c[j] - c[j - 1]) / (tg[j] - tg[j - 1]);
+                    u[j] = (6. * u[j] / (tg[j + 1] - tg[j - 1]) - sig * u[j - 1]) / p;
+                }
+                d2[t->jmax - 1] = 0.;
+                for (int j = t->jmax - 2; j >= 0; j--) d2[j] = d2[j] * d2[j + 1] + u[j];
+            }
+            free(u);
+        }
+        else
+            for (int i = 0; i < t->imax; i++)
+                for (int j = 0; j < t->jmax - 1; j++)
+                    t->deriv[(size_t)i * t->jmax + j] = (s->coeff[(size_t)i * t->jmax + j + 1] - s->coeff[(size_t)i * t->jmax + j])
+                                                        / (s->tgrid[j + 1] - s->tgrid[j]);
     }
     m->ndust = d->dust_ncomp;
     m->dust = (ora_dust*)calloc(m->ndust > 0 ? m->ndust : 1, sizeof(ora_dust));
@@ -314,6 +336,13 @@ static double tab_rate(const ora_table* t, int up, int low, int lo, double temp)
 {
     const size_t i = (size_t)up * (up - 1) / 2 + low;
     const double tt = temp < t->max_temp ? temp : t->max_temp;
+    if (t->interp == RT_INTERP_CUBIC_SPLINE) { /* collision_data_cub_spline::get_rate, coll_rates.cpp:121-132 */
+        const double h = t->tgrid[lo + 1] - t->tgrid[lo];
+        const double a = (t->tgrid[lo + 1] - tt) / h, b = 1. - a;
+        const double* c = t->coeff + i * t->jmax;
+        const double* s2 = t->deriv + i * t->jmax;
+        return fabs(a * c[lo] + b * c[lo + 1] + (1. / 6.) * ((a * a * a - a) * s2[lo] + (b * b * b - b) * s2[lo + 1]) * (h * h));
+    }
     return t->coeff[i * t->jmax + lo] + t->deriv[i * t->jmax + lo] * (tt - t->tgrid[lo]);
 }
 

@@ -17,6 +17,7 @@ RT_OK = 0
 RT_RULE_GENERIC, RT_RULE_CH3OH, RT_RULE_OH_HF, RT_RULE_H2O, RT_RULE_NH3, RT_RULE_H2CO = 0, 1, 2, 3, 4, 5
 RT_SCHEME_LVG, RT_SCHEME_LINE_OVERLAP = 0, 1
 RT_START_GIVEN, RT_START_BOUNDARY, RT_START_LTE, RT_START_CHAINED = 0, 1, 2, 3
+RT_INTERP_LINEAR, RT_INTERP_CUBIC_SPLINE = 0, 1
 
 c_double_p = C.POINTER(C.c_double)
 c_int_p = C.POINTER(C.c_int)
@@ -33,7 +34,8 @@ class rt_params(C.Structure):
 
 
 class rt_coll_table(C.Structure):
-    _fields_ = [("nb_lev", C.c_int), ("jmax", C.c_int), ("tgrid", c_double_p), ("coeff", c_double_p)]
+    _fields_ = [("nb_lev", C.c_int), ("jmax", C.c_int), ("tgrid", c_double_p), ("coeff", c_double_p),
+                ("interp", C.c_int), ("reserved0", C.c_int)]
 
 
 class rt_dust_comp(C.Structure):
@@ -114,6 +116,7 @@ class CollTable:
     nb_lev: int
     tgrid: np.ndarray  # [jmax]
     coeff: np.ndarray  # [imax, jmax]
+    interp: int = 0    # RT_INTERP_LINEAR / RT_INTERP_CUBIC_SPLINE (collision_data_cub_spline, coll_rates.cpp:89-132)
 
 
 @dataclass
@@ -214,6 +217,7 @@ class Problem:
             assert co.shape == (t.nb_lev * (t.nb_lev - 1) // 2, tg.shape[0])
             hold += [tg, co]
             tarr[k].nb_lev, tarr[k].jmax, tarr[k].tgrid, tarr[k].coeff = t.nb_lev, tg.shape[0], dptr(tg), dptr(co)
+            tarr[k].interp = int(getattr(t, "interp", 0))
         hold.append(tarr); d.tables = tarr
         d.scheme = self.scheme
         if self.line_groups is not None:

@@ -15,6 +15,15 @@ __device__ __forceinline__ double tab_rate(const DevTable& t, int up, int low, i
     // collision_data::get_rate(first, sec, lo, temp), coll_rates.cpp:54-59, temp clamped by the caller (:188)
     const size_t p = (size_t)up * (up - 1) / 2 + low;
     const double tt = temp < t.max_temp ? temp : t.max_temp;
+    if (t.interp == RT_INTERP_CUBIC_SPLINE) {
+        // collision_data_cub_spline::get_rate, coll_rates.cpp:121-132 (lo <= jmax - 2 by collision_data::locate)
+        const double h = t.tgrid[lo + 1] - t.tgrid[lo];
+        const double a = (t.tgrid[lo + 1] - tt) / h;
+        const double b = 1. - a;
+        const double c0 = t.coeff_t[(size_t)lo * t.imax + p], c1 = t.coeff_t[(size_t)(lo + 1) * t.imax + p];
+        const double s0 = t.deriv_t[(size_t)lo * t.imax + p], s1 = t.deriv_t[(size_t)(lo + 1) * t.imax + p];
+        return fabs(a * c0 + b * c1 + (1. / 6.) * ((a * a * a - a) * s0 + (b * b * b - b) * s1) * (h * h));
+    }
     return t.coeff_t[(size_t)lo * t.imax + p] + t.deriv_t[(size_t)lo * t.imax + p] * (tt - t.tgrid[lo]);
 }
 

@@ -455,7 +455,11 @@ __global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trs
 // NST stages of K columns each (kk0, kk0 + K, ...): the accumulators stay in registers across the stages, so a 128-deep
 // update (K = 64, NST = 2) reads and writes C once -- half the C traffic per flop of two 64-deep updates -- while the
 // A / B tiles of one stage still fit three CTAs per SM.
-template <int K, int ROWS, int NST, int MINB = (ROWS == 64 ? 3 : 2)>
+// CST: the C tile does not pass through registers on the way in: it is staged into shared memory by cp.async (its own
+// commit group, behind the first A / B stage), the accumulators start at zero, and D = C + (-A B) is formed in the epilogue.
+// The warp never waits for C: its HBM latency hides behind the whole product instead of preceding it.
+#define GM_LDC 72 // row stride of the staged C tile: = 8 (mod 16) doubles -> conflict-free 16-byte reads in the epilogue
+template <int K, int ROWS, int NST, int MINB = (ROWS == 64 ? 3 : 2), bool CST = false>
 __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
     const int a = a0 + blockIdx.z;
@@ -487,7 +491,17 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
         asm volatile("cp.async.commit_group;");
     };
     stage(kk0);
-    // ---- accumulators <- C
+    double* Cs = Bs + K * GM_LDB; // [ROWS][GM_LDC] (CST only)
+    if constexpr (CST) {
+        for (int e = tid; e < ROWS * (GM_COLS / 2); e += ROWS * 2) {
+            const int r = e >> 5, ch = e & 31;
+            double* dst = Cs + r * GM_LDC + 2 * ch;
+            if (r0 + r < Np && cc0 + 2 * ch < c1) cp_async16(dst, A + (size_t)(r0 + r) * ld + cc0 + 2 * ch);
+            else { dst[0] = 0.; dst[1] = 0.; }
+        }
+        asm volatile("cp.async.commit_group;");
+    }
+    // ---- accumulators <- C (or zero when C is staged)
     const int wr = warp >> 1, wc = warp & 1;
     const int rw = r0 + wr * 32, cw = cc0 + wc * 32;
     const int fr = lane >> 2, fc = (lane & 3) * 2;
@@ -497,7 +511,7 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
 #pragma unroll
         for (int tj = 0; tj < 4; tj++) {
             const int r = rw + ti * 8 + fr, c = cw + tj * 8 + fc;
-            if (r < Np && c < c1) {
+            if (!CST && r < Np && c < c1) {
                 const double2 v = *reinterpret_cast<const double2*>(A + (size_t)r * ld + c);
                 acc[ti][tj][0] = v.x; acc[ti][tj][1] = v.y;
             }
@@ -511,7 +525,8 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
             __syncthreads(); // every warp is done with the previous stage's tiles
             stage(kk0 + st * K);
         }
-        asm volatile("cp.async.wait_group 0;");
+        if (CST && st == 0) asm volatile("cp.async.wait_group 1;"); // the first A / B stage; C may still be in flight
+        else asm volatile("cp.async.wait_group 0;");
         __syncthreads();
 #pragma unroll 4
         for (int k4 = 0; k4 < K / 4; k4++) {
@@ -526,12 +541,22 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
                 for (int tj = 0; tj < 4; tj++) dmma884(acc[ti][tj][0], acc[ti][tj][1], af[ti], bf[tj]);
         }
     }
+    if constexpr (CST) {
+        if (NST == 1) { asm volatile("cp.async.wait_group 0;"); __syncthreads(); } // NST > 1: the last stage's wait covered C
+    }
 #pragma unroll
     for (int ti = 0; ti < 4; ti++)
 #pragma unroll
         for (int tj = 0; tj < 4; tj++) {
             const int r = rw + ti * 8 + fr, c = cw + tj * 8 + fc;
-            if (r < Np && c < c1) *reinterpret_cast<double2*>(A + (size_t)r * ld + c) = make_double2(acc[ti][tj][0], acc[ti][tj][1]);
+            if (r < Np && c < c1) {
+                double2 v = make_double2(acc[ti][tj][0], acc[ti][tj][1]);
+                if constexpr (CST) {
+                    const double2 cv = *reinterpret_cast<const double2*>(Cs + (wr * 32 + ti * 8 + fr) * GM_LDC + wc * 32 + tj * 8 + fc);
+                    v.x += cv.x; v.y += cv.y;
+                }
+                *reinterpret_cast<double2*>(A + (size_t)r * ld + c) = v;
+            }
         }
 }
 
@@ -676,6 +701,7 @@ static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk
     else if (K == 64) {
         if (g_gemm_mode == 0) k_gemm<64, 128, 1><<<grid, 256, sm128, s>>>(d, i0, kk0, c0, c1, a0, a1);
         else if (g_gemm_mode == 1) k_gemm<64, 64, 1><<<g64, 128, sm64, s>>>(d, i0, kk0, c0, c1, a0, a1);
+        else if (g_gemm_mode == 4) k_gemm<32, 64, 2, 3, true><<<g64, 128, (64 * 36 + 32 * GM_LDB + 64 * GM_LDC) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
         else k_gemm<32, 64, 2, 4><<<g64, 128, (64 * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
     }
     else {
@@ -867,5 +893,6 @@ cudaError_t lu_kernels_init()
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 64, 1>, at, sm64);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 64, 2>, at, sm64);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 4>, at, (64 * 36 + 32 * GM_LDB) * (int)sizeof(double));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 2, 3, true>, at, (64 * 36 + 32 * GM_LDB + 64 * GM_LDC) * (int)sizeof(double));
     return e;
 }

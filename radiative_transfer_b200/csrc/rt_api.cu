@@ -108,7 +108,7 @@ const char* rt_status_string(rt_status s)
 }
 
 const char* rt_last_error(const rt_model* m) { return m ? m->last_error.c_str() : g_create_error.c_str(); }
-int rt_abi_version(void) { return 4; }
+int rt_abi_version(void) { return 5; }
 
 } // extern "C"
 
@@ -304,13 +304,35 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
         T.nb_lev = t.nb_lev; T.jmax = t.jmax; T.imax = t.nb_lev * (t.nb_lev - 1) / 2;
         if (t.jmax < 2 || t.nb_lev < 2 || t.nb_lev > N) { g_create_error = "bad collision table"; rt_model_destroy(m); return RT_ERR_INVALID; }
         T.max_temp = t.tgrid[t.jmax - 1];
+        T.interp = t.interp;
+        if (t.interp != RT_INTERP_LINEAR && t.interp != RT_INTERP_CUBIC_SPLINE) { g_create_error = "bad rt_coll_table::interp"; rt_model_destroy(m); return RT_ERR_INVALID; }
         std::vector<double> ct((size_t)T.imax * T.jmax), dt((size_t)T.imax * T.jmax, 0.);
-        for (int i = 0; i < T.imax; i++)
+        std::vector<double> u(T.jmax), d2(T.jmax);
+        for (int i = 0; i < T.imax; i++) {
+            const double* c = t.coeff + (size_t)i * T.jmax;
+            const double* tg = t.tgrid;
             for (int j = 0; j < T.jmax; j++) {
-                ct[(size_t)j * T.imax + i] = t.coeff[(size_t)i * T.jmax + j];
-                if (j < T.jmax - 1)
-                    dt[(size_t)j * T.imax + i] = (t.coeff[(size_t)i * T.jmax + j + 1] - t.coeff[(size_t)i * T.jmax + j]) / (t.tgrid[j + 1] - t.tgrid[j]);
+                ct[(size_t)j * T.imax + i] = c[j];
+                if (t.interp == RT_INTERP_LINEAR && j < T.jmax - 1)
+                    dt[(size_t)j * T.imax + i] = (c[j + 1] - c[j]) / (tg[j + 1] - tg[j]);
             }
+            if (t.interp == RT_INTERP_CUBIC_SPLINE) {
+                // collision_data_cub_spline::calc_coeff_deriv, coll_rates.cpp:89-119: natural cubic spline, tridiagonal sweep
+                // in the reference's expression order
+                const int jm = T.jmax;
+                d2[0] = u[0] = 0.;
+                for (int j = 1; j < jm - 1; j++) {
+                    const double sig = (tg[j] - tg[j - 1]) / (tg[j + 1] - tg[j - 1]);
+                    const double p = sig * d2[j - 1] + 2.;
+                    d2[j] = (sig - 1.) / p;
+                    u[j] = (c[j + 1] - c[j]) / (tg[j + 1] - tg[j]) - (c[j] - c[j - 1]) / (tg[j] - tg[j - 1]);
+                    u[j] = (6. * u[j] / (tg[j + 1] - tg[j - 1]) - sig * u[j - 1]) / p;
+                }
+                d2[jm - 1] = 0.;
+                for (int j = jm - 2; j >= 0; j--) d2[j] = d2[j] * d2[j + 1] + u[j];
+                for (int j = 0; j < jm; j++) dt[(size_t)j * T.imax + i] = d2[j];
+            }
+        }
         T.tgrid = dev_upload(m, t.tgrid, T.jmax, false);
         T.coeff_t = dev_upload(m, ct.data(), ct.size(), false);
         T.deriv_t = dev_upload(m, dt.data(), dt.size(), false);

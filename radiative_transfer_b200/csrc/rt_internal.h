@@ -27,7 +27,7 @@
 #define RT_AFF_STRIDE 132 // {n_aff, pad, pad, pad, pos[64], cur[64]}
 
 struct DevTable {            // one collision_data, transposed to [jmax][imax] so one layer's T-row is contiguous
-    int nb_lev, jmax, imax, pad;
+    int nb_lev, jmax, imax, interp; // interp: RT_INTERP_* (cubic spline: deriv_t holds the SECOND derivatives)
     double max_temp;
     const double* tgrid;     // [jmax]
     const double* coeff_t;   // [jmax][imax]

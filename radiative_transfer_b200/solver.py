@@ -18,7 +18,7 @@ from . import abi
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_B200_LIB", os.path.join(HERE, "librt_b200.so"))  # override: kernel-variant experiments only
 _lib = None
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 ENTRY_POINTS = [
     "rt_params_default", "rt_status_string", "rt_last_error", "rt_abi_version", "rt_model_create", "rt_model_destroy",

@@ -407,9 +407,15 @@ def small(name: str, L: int = 6) -> Problem:
         return config_nh3(L=L)
     if name == "h2co":
         return config_h2co(L=L)
-    if name == "generic":
+    if name in ("generic", "generic_spline"):
         p = config_ch3oh(L=L, n_vt=1, n_k=5, n_j=6)  # N = 30
         p.species_rule = RT_RULE_GENERIC
         p.mol_name = "synthetic"
+        if name == "generic_spline":
+            # the cubic-spline table class collision_data_cub_spline (coll_rates.cpp:89-132) for two of
+            # the three tables, the third stays linear (both classes side by side in one collisional_transitions)
+            p.name = "generic_spline"
+            p.tables[0].interp = 1
+            p.tables[2].interp = 1
         return p
     raise KeyError(name)

@@ -17,6 +17,7 @@ CASES = {  # name -> (synthetic.small name, layers)
     "h2o_small": ("h2o_small", 2),
     "nh3": ("nh3", 3),     # nh3_collisions / h2co_collisions mixing rules
     "h2co": ("h2co", 3),
+    "generic_spline": ("generic_spline", 3),  # f-3: collision_data_cub_spline tables (coll_rates.cpp:89-132)
 }
 
 
@@ -32,6 +33,8 @@ def problem_digest(p) -> str:
     arrs = [p.energy, p.g, p.v, p.j, p.einst, p.lvg_delta, p.lvg_gamma, p.lvg_p]
     for t in p.tables:
         arrs += [t.tgrid, t.coeff]
+        if getattr(t, "interp", 0):
+            arrs.append(np.array([t.interp], dtype=np.int64))
     for c in p.dust:
         arrs += [c.ph_en, c.abs_coeff, np.array([c.wvl_exp])]
     for o in (p.overlap1, p.overlap2):
