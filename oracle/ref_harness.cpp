@@ -794,7 +794,7 @@ int ref_adapter_roundtrip(const rt_model_desc* d, const rt_layer_soa* lay)
     for (int i = 0; i < N; i++) bad += (q.g[i] != d->g[i]) + (d->v && q.v[i] != d->v[i]) + (d->j && q.j[i] != d->j[i]);
     bad += (q.mol_mass != d->mol_mass);
     for (int k = 0; k < q.nb_neutral_tables + q.nb_electron_tables; k++) {
-        if (q.tables[k].nb_lev != d->tables[k].nb_lev || q.tables[k].jmax != d->tables[k].jmax) { delete c; return -1; }
+        if (q.tables[k].nb_lev != d->tables[k].nb_lev || q.tables[k].jmax != d->tables[k].jmax || q.tables[k].interp != d->tables[k].interp) { delete c; return -1; }
         cmp(q.tables[k].tgrid, d->tables[k].tgrid, q.tables[k].jmax);
         cmp(q.tables[k].coeff, d->tables[k].coeff, (size_t)q.tables[k].jmax * q.tables[k].nb_lev * (q.tables[k].nb_lev - 1) / 2);
     }

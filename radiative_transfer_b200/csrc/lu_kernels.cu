@@ -29,9 +29,6 @@
 #define PNL_BIG_R 3     // rows per thread x threads of the kernel variant for 512 < m <= 768
 #define PNL_BIG_NT 256
 #endif
-#ifndef PNL_DEBUG_JB0
-#define PNL_DEBUG_JB0 0 // development: 32 skips the column loop (times the panel's load / store alone; wrong results)
-#endif
 #ifndef PNL_JB
 #define PNL_JB 8   // columns per unrolled block of the panel's column loop
 #endif
@@ -114,16 +111,12 @@ __global__ void __launch_bounds__(NT, (R * NT <= 384 ? 2 : 1)) k_panel(DevModel 
 
     // panel -> staging tile with 8-byte cp.async (the tile's row stride of 33 doubles is not 16-byte aligned): every
     // thread has all of its m / 8 copies in flight at once
-#ifndef PNL_DIRECT_LOAD
     for (int r = warp; r < m; r += NT / 32) cp_async8(s_tile + r * 33 + lane, A + (size_t)(k0 + r) * ld + k0 + lane);
     asm volatile("cp.async.commit_group;" ::: "memory");
-#endif
     for (int r = t; r < m; r += NT) s_slot[r] = (short)(r < 32 ? r : -1);
     if (t < 32) { s_pos[t] = t; s_cur[t] = t; }
     if (t == 0) s_naff = 32;
-#ifndef PNL_DIRECT_LOAD
     asm volatile("cp.async.wait_group 0;" ::: "memory");
-#endif
     __syncthreads();
 
     // Rows never move between threads: vp[i] is the CURRENT position of the row held in x[i] (the position the
@@ -134,23 +127,12 @@ __global__ void __launch_bounds__(NT, (R * NT <= 384 ? 2 : 1)) k_panel(DevModel 
     for (int i = 0; i < R; i++) {
         const int r = t + NT * i;
         vp[i] = r < m ? r : -1;
-#ifdef PNL_DIRECT_LOAD
-        // every thread reads its own rows (256 contiguous bytes each) straight into registers: 16 independent 16-byte loads
-        // per row in flight, no shared-memory round trip
-        const double2* src = reinterpret_cast<const double2*>(A + (size_t)(k0 + (r < m ? r : 0)) * ld + k0);
-#pragma unroll
-        for (int c = 0; c < 16; c++) {
-            const double2 v = r < m ? src[c] : make_double2(0., 0.);
-            x[i][2 * c] = v.x; x[i][2 * c + 1] = v.y;
-        }
-#else
 #pragma unroll
         for (int c = 0; c < 32; c++) x[i][c] = r < m ? s_tile[r * 33 + c] : 0.;
-#endif
     }
 
 #pragma unroll 1
-    for (int jb = PNL_DEBUG_JB0; jb < 32; jb += 8) {
+    for (int jb = 0; jb < 32; jb += 8) {
 #pragma unroll
         for (int jj = 0; jj < 8; jj++) {
             const int j = jb + jj;
@@ -440,21 +422,20 @@ __global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trs
 
 // ------------------------------------------------------------------------------------------------------------
 // Trailing update on the FP64 tensor cores:  C[i0.., c0..c1) -= A[i0.., kk0..kk0+K) * A[kk0..kk0+K, c0..c1),
-// K = 32 or 64.  CTA tile 128 x 64, 8 warps (4 x 2), warp tile 32 x 32 = 4 x 4 DMMA m8n8k4 tiles, accumulators
-// initialised with C (so the epilogue is a plain store of -(-C + AB) ... i.e. we accumulate D = C - A*B by feeding
-// the NEGATED A fragment).  A and B tiles are staged once in shared memory with cp.async (K <= 64: no k-loop
-// pipeline needed; two CTAs per SM overlap one CTA's loads with the other's math).
+// K = 32 or 64.  CTA tile 64 x 64, 4 warps (2 x 2), warp tile 32 x 32 = 4 x 4 DMMA m8n8k4 tiles (SASS DMMA.8x8x4; the
+// m16n8k8 / m16n8k16 f64 shapes of mma.sync compile to the same DMMA.8x8x4 sequence on sm_100a -- checked with cuobjdump --
+// so they save no issue slots), accumulators initialised with C; D = C - A*B is accumulated by feeding the NEGATED A
+// fragment.  A and B tiles are staged in shared memory with 16-byte cp.async, a 64-deep update as two 32-deep stages
+// through the same buffer: four CTAs per SM overlap one CTA's loads and stores with the others' DMMA stream.
 // Shared-memory strides are = 4 (mod 16) doubles so that every fragment load is bank-conflict free:
 //   A fragment: lane holds As[row = lane/4][k = lane%4]   (row-major tile, stride K+4)
 //   B fragment: lane holds Bs[k = lane%4][col = lane/4]   (row-major tile, stride 68)
 // ------------------------------------------------------------------------------------------------------------
-#define GM_ROWS 128
 #define GM_COLS 64
 #define GM_LDB 68
 
-// NST stages of K columns each (kk0, kk0 + K, ...): the accumulators stay in registers across the stages, so a 128-deep
-// update (K = 64, NST = 2) reads and writes C once -- half the C traffic per flop of two 64-deep updates -- while the
-// A / B tiles of one stage still fit three CTAs per SM.
+// NST stages of K columns each (kk0, kk0 + K, ...): the accumulators stay in registers across the stages, so C is read and
+// written once per NST * K eliminated columns while one stage's A / B tiles fit four CTAs per SM.
 // CST: the C tile does not pass through registers on the way in: it is staged into shared memory by cp.async (its own
 // commit group, behind the first A / B stage), the accumulators start at zero, and D = C + (-A B) is formed in the epilogue.
 // The warp never waits for C: its HBM latency hides behind the whole product instead of preceding it.
@@ -660,18 +641,17 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
     else k_panel<PNL_BIG_R, PNL_BIG_NT><<<n, PNL_BIG_NT, smem, s>>>(d, k0, nleft, a0, a1);
 }
 
-// 64-deep trailing update.  0: 128x64 tiles, one 64-deep stage, 2 CTAs/SM (2.97 ms per N = 768 slab-iteration);
-// 1: 64x64 tiles, one stage, 3 CTAs/SM (2.87 ms); 3 (default): 64x64 tiles, TWO 32-deep stages through one 36 KB buffer
-// and 128 registers -> FOUR CTAs/SM (2.59 ms): with the update at the machine balance of L2 and the tensor pipe, a fourth
-// resident CTA covers more of the others' load / store phases than the second barrier pair costs (five CTAs/SM at 96
-// registers spill: 2.64 ms; 32 x 16 warp tiles, i.e. eight warps per CTA at 78 / 64 registers and three / four CTAs per
-// SM: 2.62 / 2.69 ms -- more resident warps than 16 per SM do not help; the B tile kept resident over two row tiles,
-// 13 % less L2 traffic per flop at 53 KB / four CTAs per SM: 2.88 ms -- the longer serial life of a CTA costs more than the
-// traffic saves).  A persistent, cp.async
-// double-buffered variant with C prefetch was measured 25 % SLOWER (3.6 vs 2.9 ms per slab-iteration): at K = 64 the
-// update moves 224 KB per tile through L2 for 4 us of DMMA work, i.e. ~8 TB/s chip-wide -- it is L2-bandwidth-bound,
-// not latency-bound, so deeper pipelining does not help.  A second attempt -- K cut into stages of 32, cp.async double
-// buffering inside the CTA, still 3 CTAs/SM -- was also slower (2.54 vs 2.47 ms at K = 128, 3.14 vs 2.88 ms at K = 64).
+// 64-deep trailing update: 64 x 64 tiles, TWO 32-deep stages through one 36 KB buffer, 128 registers -> FOUR CTAs/SM
+// (2.55 ms per N = 768 slab-iteration).  Measured and removed (same step): 128 x 64 tiles, one 64-deep stage, 2 CTAs/SM
+// 2.97 ms; 64 x 64, one stage, 3 CTAs/SM 2.87 ms; five CTAs/SM at 96 registers (spills) 2.64 ms; 32 x 16 warp tiles, eight
+// warps per CTA 2.62 - 2.69 ms; B tile resident over two row tiles (-13 % L2 traffic, 53 KB) 2.88 ms; a persistent
+// cp.async double-buffered kernel with C prefetch 3.6 ms; K cut into 32-deep stages double-buffered inside the CTA at
+// 3 CTAs/SM 3.14 ms; 128-wide super-blocks (third blocking level: 128-deep update 2.47 ms but +0.27 ms TRSM, +0.04 ms
+// panel: 5.42 vs 5.52 ms per full-batch iteration, slower with few active layers); round 2: the C tile staged by cp.async
+// (RT_B200_GEMM_MODE=4, accumulators start at zero, the warp never waits for C) at 73 KB / 3 CTAs/SM: 2.91 ms -- in every
+// case the fourth resident CTA is worth more than what the variant saves; `prefetch.global.L2` of the C tile of the CTA that
+// runs 148 / 296 / 592 / 1184 block indices later (so that a tile's C loads hit L2 instead of HBM): 2.58 ms at every
+// distance against 2.53 ms without -- the update is not waiting for C.
 static int g_gemm_mode = 3;
 // Layer groups of one solve (development switch RT_B200_LU_GROUPS).  The layers of a batch are independent, so the
 // active list is cut into G slices whose factorisations run on G streams: while one slice sits in a latency-bound
@@ -679,35 +659,18 @@ static int g_gemm_mode = 3;
 // slices fill the idle SMs.
 static int g_lu_groups = 2;
 static int g_lu_lookahead = 1; // development switch RT_B200_LU_LOOKAHEAD=0: every group on one stream
-// 128-wide super-blocks (third blocking level, RT_B200_LU_SUPER=1).  Measured at N = 768, 200 layers: the 128-deep
-// trailing update reads and writes C half as often and runs at 2.47 instead of 2.87 ms per slab-iteration, but 4 GFLOP of
-// the update move into the TRSM's left update (0.68 -> 0.95 ms) and the panel's wider interchange costs 0.04 ms: 5.42 vs
-// 5.52 ms per full-batch iteration, and SLOWER with few active layers (60 layers: 2.43 vs 2.35 ms), so the converged
-// CH3OH solve takes 210 instead of 207 ms.  Off by default; kept as a tested switch (tests/test_gpu_parity.py).
-static int g_lu_super = 0;
 static int g_lu_group_min = 48; // layers per slice below which a slice no longer fills its share of the machine: fewer groups
 
-// K = 32: next panel's columns; 64: trailing update of a 64-wide block; 128: of a 128-wide super-block (two 64-deep stages)
+// K = 32: next panel's columns; 64: trailing update of a 64-wide block
 static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
     const int n = a1 - a0;
-    const dim3 grid((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + GM_ROWS - 1) / GM_ROWS, n);
     const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, n);
-    const size_t sm128 = (GM_ROWS * 68 + 64 * GM_LDB) * sizeof(double), sm64 = (64 * 68 + 64 * GM_LDB) * sizeof(double);
+    const size_t smem = (64 * 36 + 32 * GM_LDB) * sizeof(double);
     g_rt_launches++;
-    if (K == 32) { // next panel's 32 columns: 64 x 64 tiles at four CTAs/SM (128 x 64 at two: 0.5 % slower per slab-iteration)
-        k_gemm<32, 64, 1, 4><<<g64, 128, (64 * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
-    }
-    else if (K == 64) {
-        if (g_gemm_mode == 0) k_gemm<64, 128, 1><<<grid, 256, sm128, s>>>(d, i0, kk0, c0, c1, a0, a1);
-        else if (g_gemm_mode == 1) k_gemm<64, 64, 1><<<g64, 128, sm64, s>>>(d, i0, kk0, c0, c1, a0, a1);
-        else if (g_gemm_mode == 4) k_gemm<32, 64, 2, 3, true><<<g64, 128, (64 * 36 + 32 * GM_LDB + 64 * GM_LDC) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
-        else k_gemm<32, 64, 2, 4><<<g64, 128, (64 * 36 + 32 * GM_LDB) * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
-    }
-    else {
-        if (g_gemm_mode == 0) k_gemm<64, 128, 2><<<grid, 256, sm128, s>>>(d, i0, kk0, c0, c1, a0, a1);
-        else k_gemm<64, 64, 2><<<g64, 128, sm64, s>>>(d, i0, kk0, c0, c1, a0, a1);
-    }
+    if (K == 32) k_gemm<32, 64, 1, 4><<<g64, 128, smem, s>>>(d, i0, kk0, c0, c1, a0, a1);
+    else if (g_gemm_mode == 4) k_gemm<32, 64, 2, 3, true><<<g64, 128, smem + 64 * GM_LDC * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
+    else k_gemm<32, 64, 2, 4><<<g64, 128, smem, s>>>(d, i0, kk0, c0, c1, a0, a1);
 }
 
 void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
@@ -747,8 +710,10 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
     // columns [c0, c1) right of the panel at k0: left update nleft_lo wide left of c_split, nleft_hi wide from c_split on
     auto trsm_on = [&](cudaStream_t ss, int g, int k0, int c0, int c1, int nleft_lo, int nleft_hi, int c_split) {
         const double nc = c1 - c0, ncl = std::max(0, std::min(c_split, c1) - c0), nch = nc - ncl;
-        rt_prof_begin(m, c_trsm, ss, 32. * 32. * nc + 2. * 32. * (nleft_lo * ncl + nleft_hi * nch),
-                      16. * 32. * nc + 8. * (nleft_lo * ncl + nleft_hi * nch));
+        // algorithmic columns only: of the 32 columns of padding right of the matrix one (the right-hand side) is real
+        const double pad = c1 > Np + 1 ? c1 - (Np + 1) : 0., nca = nc - pad, ncha = nch - pad;
+        rt_prof_begin(m, c_trsm, ss, 32. * 32. * nca + 2. * 32. * (nleft_lo * ncl + nleft_hi * ncha),
+                      16. * 32. * nca + 8. * (nleft_lo * ncl + nleft_hi * ncha));
         g_rt_launches++;
         const dim3 grid((c1 - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]);
         if (nleft_hi > 0) k_trsm<true><<<grid, TRSM_THREADS, trsm_smem_bytes(nleft_hi), ss>>>(d, k0, c0, c1, nleft_lo, nleft_hi, c_split, ga0[g], ga1[g]);
@@ -757,7 +722,8 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
     };
     auto trsm = [&](int g, int k0, int nleft_lo, int nleft_hi, int c_split) { trsm_on(st[g], g, k0, k0 + 32, ld, nleft_lo, nleft_hi, c_split); };
     auto gemm_on = [&](cudaStream_t ss, int g, int K, int i0, int kk0, int c0, int c1) {
-        const double mr = Np - i0, nc = c1 - c0;
+        // algorithmic columns only (matrix + right-hand side), not the zero padding of ld = Np + 32
+        const double mr = Np - i0, nc = (c1 > Np + 1 ? Np + 1 : c1) - c0;
         rt_prof_begin(m, c_gemm, ss, 2. * K * mr * nc, 16. * mr * nc + 8. * K * (mr + nc));
         launch_gemm(d, ss, K, i0, kk0, c0, c1, ga0[g], ga1[g]);
         rt_prof_end(m, c_gemm, ss);
@@ -772,7 +738,7 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
     //   T:            trsm [k0+64,ld)                                                       gemm64 [k0+128,ld)    trsm [k0+128,ld) ...
     // With few active layers (the tail of a solve: every launch is far from filling the GPU) the chain of one block
     // shrinks from panel+trsm+gemm32+panel+trsm+gemm64 to panel+trsm(32 columns)+gemm32+panel+trsm+gemm64(64 columns).
-    if (g_lu_lookahead && !g_lu_super && !m->prof_timing) {
+    if (g_lu_lookahead && !m->prof_timing) {
         bool ok = true;
         for (int g = 0; g < G && ok; g++) {
             if (m->lu_side[g]) continue;
@@ -818,15 +784,9 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
             goto back_substitution;
         }
     }
-    // Three blocking levels: panels of 32 columns inside blocks of 64 inside SUPER-BLOCKS of 128 (g_lu_super; while at
-    // least 128 columns remain).  Inside a super-block at k0 the update of the columns right of it is deferred: the
-    // four panels' TRSMs subtract the pending part L_left U themselves (32 rows each), the block-level update touches
-    // only the super-block's own columns, and ONE 128-deep trailing update follows -- C is read and written once per
-    // 128 eliminated columns instead of once per 64.  The groups' launches are issued interleaved, step by step, so
-    // that every stream always has work queued.
-    for (int k0 = 0; k0 < Np;) {
-        const bool super = g_lu_super && Np - k0 >= 128;
-        const int cend = super ? k0 + 128 : ld; // columns the block-level (64-deep) update covers
+    // single stream per group (profiling pass, RT_B200_LU_LOOKAHEAD=0): the groups' launches are issued interleaved, step by
+    // step, so that every stream always has work queued
+    for (int k0 = 0; k0 < Np; k0 += 64) {
         for (int g = 0; g < G; g++) {
             set_layers(g);
             panel(g, k0, 0);
@@ -838,23 +798,9 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
                 set_layers(g);
                 panel(g, k0 + 32, 32);
                 trsm(g, k0 + 32, 32, 32, ld);
-                if (k0 + 64 < Np) gemm(g, 64, k0 + 64, k0, k0 + 64, cend);
+                if (k0 + 64 < Np) gemm(g, 64, k0 + 64, k0, k0 + 64, ld);
             }
         }
-        if (!super) { k0 += 64; continue; }
-        for (int g = 0; g < G; g++) {
-            set_layers(g);
-            panel(g, k0 + 64, 64);
-            trsm(g, k0 + 64, 0, 64, k0 + 128); // the super-block's own columns have the first block's update already
-            gemm(g, 32, k0 + 96, k0 + 64, k0 + 96, k0 + 128);
-        }
-        for (int g = 0; g < G; g++) {
-            set_layers(g);
-            panel(g, k0 + 96, 96);
-            trsm(g, k0 + 96, 96, 96, ld);
-            if (k0 + 128 < Np) gemm(g, 128, k0 + 128, k0, k0 + 128, ld);
-        }
-        k0 += 128;
     }
 back_substitution:
     for (int g = 0; g < G; g++) {
@@ -877,22 +823,18 @@ cudaError_t lu_kernels_init()
 {
     if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switches
     if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
-    if (const char* gs = getenv("RT_B200_LU_SUPER")) g_lu_super = atoi(gs);
     if (const char* gp = getenv("RT_B200_PANEL_192")) g_panel_192 = atoi(gp);
     if (const char* gq = getenv("RT_B200_LU_GROUP_MIN")) g_lu_group_min = std::max(1, atoi(gq));
     if (const char* gl = getenv("RT_B200_LU_LOOKAHEAD")) g_lu_lookahead = atoi(gl);
-    const int sm128 = (GM_ROWS * 68 + 64 * GM_LDB) * (int)sizeof(double), sm64 = (64 * 68 + 64 * GM_LDB) * (int)sizeof(double);
+    const int smg = (64 * 36 + 32 * GM_LDB) * (int)sizeof(double);
     const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
     cudaError_t e = cudaFuncSetAttribute(k_panel<1, 256>, at, 256 * 33 * (int)sizeof(double));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<2, 256>, at, 512 * 33 * (int)sizeof(double));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<2, 192>, at, 384 * 33 * (int)sizeof(double));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<PNL_BIG_R, PNL_BIG_NT>, at, 768 * 33 * (int)sizeof(double));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm<true>, at, (int)trsm_smem_bytes(96));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 128, 1>, at, sm128);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 128, 2>, at, sm128);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 64, 1>, at, sm64);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<64, 64, 2>, at, sm64);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 4>, at, (64 * 36 + 32 * GM_LDB) * (int)sizeof(double));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 2, 3, true>, at, (64 * 36 + 32 * GM_LDB + 64 * GM_LDC) * (int)sizeof(double));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm<true>, at, (int)trsm_smem_bytes(32));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 4>, at, smg);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 2, 4>, at, smg);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 2, 3, true>, at, smg + 64 * GM_LDC * (int)sizeof(double));
     return e;
 }

@@ -21,7 +21,7 @@ def adapter():
     return C.CDLL(SO)
 
 
-@pytest.mark.parametrize("name", ["generic", "oh", "oh_overlap", "ch3oh_small", "h2o_small", "nh3", "h2co"])
+@pytest.mark.parametrize("name", ["generic", "generic_spline", "oh", "oh_overlap", "ch3oh_small", "h2o_small", "nh3", "h2co"])
 def test_flatten_round_trip(adapter, problems, name):
     p = problems(name, 3)
     d, h1 = p.desc()
@@ -30,7 +30,7 @@ def test_flatten_round_trip(adapter, problems, name):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name,chained", [("ch3oh_small", True), ("oh_overlap", False), ("generic", True), ("h2o_small", False)])
+@pytest.mark.parametrize("name,chained", [("ch3oh_small", True), ("oh_overlap", False), ("generic", True), ("generic_spline", False), ("h2o_small", False)])
 def test_reference_objects_through_adapter_on_gpu(adapter, ref, problems, name, chained):
     from radiative_transfer_b200 import abi
     p = problems(name, 3)

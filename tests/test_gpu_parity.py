@@ -399,36 +399,6 @@ def test_full_size_h2o_properties(solver_mod, best_checker):
 
 
 @pytest.mark.gpu
-def test_super_block_lu_switch(problems):
-    """RT_B200_LU_SUPER=1 (128-wide super-blocks, third blocking level of the LU; off by default, lu_kernels.cu): the
-    switch is read once per process, so the check runs in a child process -- one calc_new_pop of a CH3OH-like slab
-    (N = 240, Np = 256: two super-blocks) and of an H2O-like slab (Np with a 32-column remainder) must agree with the default
-    blocking to rounding."""
-    import os, subprocess, sys, json
-    code = (
-        "import sys, json, numpy as np; sys.path.insert(0, %r)\n"
-        "from radiative_transfer_b200 import solver, synthetic\n"
-        "out = {}\n"
-        "for name, p in (('ch3oh', synthetic.small('ch3oh_mid', 5)), ('h2o', synthetic.config_h2o(L=4, N=290))):\n"
-        "    m = solver.Model(p); b = m.boundary_layer_populations(); new, eq = m.calc_new_pop(b); m.close()\n"
-        "    out[name] = [p.N, new.tolist()]\n"
-        "print(json.dumps(out))\n" % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-    res = {}
-    for sw in ("0", "1"):
-        env = dict(os.environ, RT_B200_LU_SUPER=sw)
-        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
-        assert r.returncode == 0, r.stderr[-2000:]
-        res[sw] = json.loads(r.stdout.strip().splitlines()[-1])
-    for name in res["0"]:
-        n0, a = res["0"][name]
-        n1, b = res["1"][name]
-        a, b = np.asarray(a), np.asarray(b)
-        assert n0 == n1 and a.shape == b.shape
-        assert np.allclose(a.sum(axis=1), 1.0, atol=1e-9) and np.allclose(b.sum(axis=1), 1.0, atol=1e-9)
-        assert rel_err(a, b, 1e-30) < 1e-8, name
-
-
-@pytest.mark.gpu
 def test_h2o_22ghz_gain_width(solver_mod, best_checker, problems):
     """rt_set_gain_width_line: the oH2O 6_16 -> 5_23 special line width of calc_gain (transition_data.cpp:249-260)."""
     p = problems("h2o_small", 4)
