@@ -2,7 +2,7 @@
 # GPU call D: whole GPU suite with the final fixtures, single-GPU bench lines of every config -> profiles/, ncu launch list +
 # full captures of the trailing update (both staging variants) with the DMMA pipe counters
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q --tb=short -p no:cacheprovider > gpurun_out/r02d_pytest_gpu.log 2>&1
+python -m pytest tests -m gpu -q --tb=short -p no:cacheprovider > gpurun_out/r02d_pytest_gpu.log 2>&1
 echo "pytest rc=$?"; tail -12 gpurun_out/r02d_pytest_gpu.log | cut -c1-300
 python bench.py --steps 10 --warmup 3 > gpurun_out/r02_bench_ch3oh_n1.json 2> gpurun_out/r02_bench_ch3oh_n1.err; echo "bench ch3oh rc=$?"
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r02_bench_ch3oh_reference_arm.json 2> gpurun_out/r02_bench_ch3oh_reference_arm.err; echo "ref arm rc=$?"

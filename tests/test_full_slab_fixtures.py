@@ -24,6 +24,10 @@ def test_fixture_matches_generator_and_is_sane(case):
     # layers the reference returns as non-finite must be on the allow-list (they cannot be compared)
     for l in np.flatnonzero(~fin):
         assert int(l) in F.ALLOW.get(case, {}), (case, int(l))
+    # the rounding-sensitivity map is there, and the slab is mostly made of layers that ARE held to 1e-6
+    assert "sens_pop" in gold and len(gold["sens_probes"]) >= 3
+    assert F.sensitive(gold).mean() <= 0.08, "too many rounding-sensitive layers: the slab would test little"
+    assert len(F.ALLOW.get(case, {})) <= 2
 
 
 @pytest.mark.parametrize("case,layers", [("oh", [0, 50, 99]), ("oh_overlap", [0, 399]), ("h2o150", [10, 150]), ("ch3oh", [60])])
