@@ -436,11 +436,7 @@ __global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trs
 
 // NST stages of K columns each (kk0, kk0 + K, ...): the accumulators stay in registers across the stages, so C is read and
 // written once per NST * K eliminated columns while one stage's A / B tiles fit four CTAs per SM.
-// CST: the C tile does not pass through registers on the way in: it is staged into shared memory by cp.async (its own
-// commit group, behind the first A / B stage), the accumulators start at zero, and D = C + (-A B) is formed in the epilogue.
-// The warp never waits for C: its HBM latency hides behind the whole product instead of preceding it.
-#define GM_LDC 72 // row stride of the staged C tile: = 8 (mod 16) doubles -> conflict-free 16-byte reads in the epilogue
-template <int K, int ROWS, int NST, int MINB = (ROWS == 64 ? 3 : 2), bool CST = false>
+template <int K, int ROWS, int NST, int MINB = (ROWS == 64 ? 3 : 2)>
 __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
     const int a = a0 + blockIdx.z;
@@ -472,17 +468,7 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
         asm volatile("cp.async.commit_group;");
     };
     stage(kk0);
-    double* Cs = Bs + K * GM_LDB; // [ROWS][GM_LDC] (CST only)
-    if constexpr (CST) {
-        for (int e = tid; e < ROWS * (GM_COLS / 2); e += ROWS * 2) {
-            const int r = e >> 5, ch = e & 31;
-            double* dst = Cs + r * GM_LDC + 2 * ch;
-            if (r0 + r < Np && cc0 + 2 * ch < c1) cp_async16(dst, A + (size_t)(r0 + r) * ld + cc0 + 2 * ch);
-            else { dst[0] = 0.; dst[1] = 0.; }
-        }
-        asm volatile("cp.async.commit_group;");
-    }
-    // ---- accumulators <- C (or zero when C is staged)
+    // ---- accumulators <- C
     const int wr = warp >> 1, wc = warp & 1;
     const int rw = r0 + wr * 32, cw = cc0 + wc * 32;
     const int fr = lane >> 2, fc = (lane & 3) * 2;
@@ -492,7 +478,7 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
 #pragma unroll
         for (int tj = 0; tj < 4; tj++) {
             const int r = rw + ti * 8 + fr, c = cw + tj * 8 + fc;
-            if (!CST && r < Np && c < c1) {
+            if (r < Np && c < c1) {
                 const double2 v = *reinterpret_cast<const double2*>(A + (size_t)r * ld + c);
                 acc[ti][tj][0] = v.x; acc[ti][tj][1] = v.y;
             }
@@ -506,8 +492,7 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
             __syncthreads(); // every warp is done with the previous stage's tiles
             stage(kk0 + st * K);
         }
-        if (CST && st == 0) asm volatile("cp.async.wait_group 1;"); // the first A / B stage; C may still be in flight
-        else asm volatile("cp.async.wait_group 0;");
+        asm volatile("cp.async.wait_group 0;");
         __syncthreads();
 #pragma unroll 4
         for (int k4 = 0; k4 < K / 4; k4++) {
@@ -522,22 +507,12 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
                 for (int tj = 0; tj < 4; tj++) dmma884(acc[ti][tj][0], acc[ti][tj][1], af[ti], bf[tj]);
         }
     }
-    if constexpr (CST) {
-        if (NST == 1) { asm volatile("cp.async.wait_group 0;"); __syncthreads(); } // NST > 1: the last stage's wait covered C
-    }
 #pragma unroll
     for (int ti = 0; ti < 4; ti++)
 #pragma unroll
         for (int tj = 0; tj < 4; tj++) {
             const int r = rw + ti * 8 + fr, c = cw + tj * 8 + fc;
-            if (r < Np && c < c1) {
-                double2 v = make_double2(acc[ti][tj][0], acc[ti][tj][1]);
-                if constexpr (CST) {
-                    const double2 cv = *reinterpret_cast<const double2*>(Cs + (wr * 32 + ti * 8 + fr) * GM_LDC + wc * 32 + tj * 8 + fc);
-                    v.x += cv.x; v.y += cv.y;
-                }
-                *reinterpret_cast<double2*>(A + (size_t)r * ld + c) = v;
-            }
+            if (r < Np && c < c1) *reinterpret_cast<double2*>(A + (size_t)r * ld + c) = make_double2(acc[ti][tj][0], acc[ti][tj][1]);
         }
 }
 
@@ -648,11 +623,11 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
 // cp.async double-buffered kernel with C prefetch 3.6 ms; K cut into 32-deep stages double-buffered inside the CTA at
 // 3 CTAs/SM 3.14 ms; 128-wide super-blocks (third blocking level: 128-deep update 2.47 ms but +0.27 ms TRSM, +0.04 ms
 // panel: 5.42 vs 5.52 ms per full-batch iteration, slower with few active layers); round 2: the C tile staged by cp.async
-// (RT_B200_GEMM_MODE=4, accumulators start at zero, the warp never waits for C) at 73 KB / 3 CTAs/SM: 2.91 ms -- in every
+// (accumulators start at zero, the warp never waits for C: long-scoreboard stalls 1.8 -> 0.8 per issue, but 73 KB -> 3 CTAs/SM
+// and the DMMA sub-pipe 74.6 % -> 64.4 % busy, profiles/r02_ncu_full_gemm_cstaged.csv): 2.91 ms -- in every
 // case the fourth resident CTA is worth more than what the variant saves; `prefetch.global.L2` of the C tile of the CTA that
 // runs 148 / 296 / 592 / 1184 block indices later (so that a tile's C loads hit L2 instead of HBM): 2.58 ms at every
 // distance against 2.53 ms without -- the update is not waiting for C.
-static int g_gemm_mode = 3;
 // Layer groups of one solve (development switch RT_B200_LU_GROUPS).  The layers of a batch are independent, so the
 // active list is cut into G slices whose factorisations run on G streams: while one slice sits in a latency-bound
 // panel (one register-file-filling CTA per SM, 200 layers = 1.35 waves on 148 SMs) the trailing updates of the other
@@ -669,7 +644,6 @@ static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk
     const size_t smem = (64 * 36 + 32 * GM_LDB) * sizeof(double);
     g_rt_launches++;
     if (K == 32) k_gemm<32, 64, 1, 4><<<g64, 128, smem, s>>>(d, i0, kk0, c0, c1, a0, a1);
-    else if (g_gemm_mode == 4) k_gemm<32, 64, 2, 3, true><<<g64, 128, smem + 64 * GM_LDC * sizeof(double), s>>>(d, i0, kk0, c0, c1, a0, a1);
     else k_gemm<32, 64, 2, 4><<<g64, 128, smem, s>>>(d, i0, kk0, c0, c1, a0, a1);
 }
 
@@ -821,7 +795,6 @@ int lu_max_np() { return PNL_MAXROWS; }
 
 cudaError_t lu_kernels_init()
 {
-    if (const char* gm = getenv("RT_B200_GEMM_MODE")) g_gemm_mode = atoi(gm); // development switches
     if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
     if (const char* gp = getenv("RT_B200_PANEL_192")) g_panel_192 = atoi(gp);
     if (const char* gq = getenv("RT_B200_LU_GROUP_MIN")) g_lu_group_min = std::max(1, atoi(gq));
@@ -835,6 +808,5 @@ cudaError_t lu_kernels_init()
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm<true>, at, (int)trsm_smem_bytes(32));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 4>, at, smg);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 2, 4>, at, smg);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 2, 3, true>, at, smg + 64 * GM_LDC * (int)sizeof(double));
     return e;
 }
