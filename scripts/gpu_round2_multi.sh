@@ -19,4 +19,4 @@ except Exception as e:
     print("unreadable", e)
 PY
 done
-tail -3 gpurun_out/r02_bench_*_n${N}_*.err | cut -c1-300
+for f in gpurun_out/r02_bench_*_n${N}_*.err; do tail -n 2 $f | cut -c1-200; done
