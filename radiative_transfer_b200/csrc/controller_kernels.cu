@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(CTL_THREADS) k_ctl_init(DevModel d, int accel)
 
 __global__ void __launch_bounds__(CTL_THREADS) k_ctl_step(DevModel d, int nlay_bound, int accel, int max_iter, double min_err)
 {
+    rt_pdl_sync();
     const int a = blockIdx.x;
     if (a >= nlay_bound || a >= *d.n_active) return;
     ctl_step_body(d, d.active[a], accel, max_iter, min_err);
@@ -37,6 +38,7 @@ __global__ void __launch_bounds__(CTL_THREADS) k_ctl_step(DevModel d, int nlay_b
 // Ordered compaction of active_flag[0..L) into active[] / n_active (single CTA; L is a few hundred).
 __global__ void __launch_bounds__(1024) k_compact(DevModel d)
 {
+    rt_pdl_sync();
     __shared__ int s_scan[1024];
     __shared__ int s_base;
     if (threadIdx.x == 0) s_base = 0;
@@ -147,9 +149,9 @@ void launch_ctl_init_flagged(const DevModel& d, cudaStream_t s, int accel) { g_r
 void launch_ctl_step(const DevModel& d, cudaStream_t s, int nlay_bound, int accel, int max_iter, double min_err)
 {
     g_rt_launches++;
-    k_ctl_step<<<nlay_bound, CTL_THREADS, 0, s>>>(d, nlay_bound, accel, max_iter, min_err);
+    rt_launch(k_ctl_step, nlay_bound, CTL_THREADS, 0, s, d, nlay_bound, accel, max_iter, min_err);
 }
-void launch_compact(const DevModel& d, cudaStream_t s) { g_rt_launches++; k_compact<<<1, 1024, 0, s>>>(d); }
+void launch_compact(const DevModel& d, cudaStream_t s) { g_rt_launches++; rt_launch(k_compact, 1, 1024, 0, s, d); }
 void launch_set_active_range(const DevModel& d, cudaStream_t s, int b, int e) { g_rt_launches++; k_set_active_range<<<(d.L + 255) / 256, 256, 0, s>>>(d, b, e); }
 void launch_set_active_failed(const DevModel& d, cudaStream_t s, int b, int e) { g_rt_launches++; k_set_active_failed<<<(d.L + 255) / 256, 256, 0, s>>>(d, b, e); }
 void launch_set_active_list(const DevModel& d, cudaStream_t s, int n)

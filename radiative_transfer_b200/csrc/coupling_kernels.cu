@@ -213,6 +213,7 @@ __device__ __forceinline__ void intensity_group(const DevModel& d, int lay, int 
 
 __global__ void __launch_bounds__(128) k_intensity(DevModel d, int nlay_bound)
 {
+    rt_pdl_sync();
     const int a = blockIdx.y;
     if (a >= nlay_bound || a >= *d.n_active) return;
     const int lay = d.active[a];
@@ -235,7 +236,7 @@ void launch_intensity(const DevModel& d, cudaStream_t s, int nlay_bound)
     if (d.G == 0) return;
     dim3 grid((d.G + 127) / 128, nlay_bound);
     g_rt_launches++;
-    k_intensity<<<grid, 128, 0, s>>>(d, nlay_bound);
+    rt_launch(k_intensity, grid, 128, 0, s, d, nlay_bound);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -324,6 +325,7 @@ __device__ __forceinline__ void atomic_max_nonneg(unsigned long long* addr, doub
 #define ASM_WARPS 8
 __global__ void __launch_bounds__(ASM_WARPS * 32) k_assemble(DevModel d, int nlay_bound, double* __restrict__ df_out)
 {
+    rt_pdl_sync();
     const int a = blockIdx.y;
     if (a >= nlay_bound || a >= *d.n_active) return;
     const int lay = d.active[a];
@@ -392,5 +394,5 @@ void launch_assemble(const DevModel& d, cudaStream_t s, int nlay_bound, double* 
 {
     dim3 grid((d.Np + ASM_WARPS - 1) / ASM_WARPS, nlay_bound);
     g_rt_launches++;
-    k_assemble<<<grid, ASM_WARPS * 32, d.Np * sizeof(double), s>>>(d, nlay_bound, df_out);
+    rt_launch(k_assemble, grid, ASM_WARPS * 32, d.Np * sizeof(double), s, d, nlay_bound, df_out);
 }

@@ -93,6 +93,7 @@ __device__ __forceinline__ void panel_rank8(double (&x)[R][32], const double* __
 template <int R, int NT>
 __global__ void __launch_bounds__(NT, (R * NT <= 384 ? 2 : 1)) k_panel(DevModel d, int k0, int nleft, int a0, int a1)
 {
+    rt_pdl_sync();
     const int a = a0 + blockIdx.x;
     if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
@@ -318,6 +319,7 @@ static size_t trsm_smem_bytes(int nleft) { return nleft > 0 ? (size_t)(32 * TRSM
 template <bool LEFT> // LEFT = false: no pending left update anywhere (first panel of a block): 128 registers, 4 CTAs/SM
 __global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trsm(DevModel d, int k0, int c0, int c_end, int nleft_lo, int nleft_hi, int c_split, int a0, int a1)
 {
+    rt_pdl_sync();
     const int a = a0 + blockIdx.y;
     if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
@@ -439,6 +441,7 @@ __global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trs
 template <int K, int ROWS, int NST, int MINB = (ROWS == 64 ? 3 : 2)>
 __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
+    rt_pdl_sync();
     const int a = a0 + blockIdx.z;
     if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
@@ -522,6 +525,7 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
 #define BS_THREADS 512
 __global__ void __launch_bounds__(BS_THREADS) k_backsolve(DevModel d, int a0, int a1)
 {
+    rt_pdl_sync();
     const int a = a0 + blockIdx.x;
     if (a >= a1 || a >= *d.n_active) return;
     const int lay = d.active[a];
@@ -610,10 +614,10 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
     const int m = d.Np - k0, n = a1 - a0;
     g_rt_launches++;
     const size_t smem = (size_t)m * 33 * sizeof(double);
-    if (m <= 256) k_panel<1, 256><<<n, 256, smem, s>>>(d, k0, nleft, a0, a1);
-    else if (m <= 384 && g_panel_192) k_panel<2, 192><<<n, 192, smem, s>>>(d, k0, nleft, a0, a1); // 170 registers: still two CTAs per SM
-    else if (m <= 512) k_panel<2, 256><<<n, 256, smem, s>>>(d, k0, nleft, a0, a1);
-    else k_panel<PNL_BIG_R, PNL_BIG_NT><<<n, PNL_BIG_NT, smem, s>>>(d, k0, nleft, a0, a1);
+    if (m <= 256) rt_launch(k_panel<1, 256>, n, 256, smem, s, d, k0, nleft, a0, a1);
+    else if (m <= 384 && g_panel_192) rt_launch(k_panel<2, 192>, n, 192, smem, s, d, k0, nleft, a0, a1); // 170 registers: still two CTAs per SM
+    else if (m <= 512) rt_launch(k_panel<2, 256>, n, 256, smem, s, d, k0, nleft, a0, a1);
+    else rt_launch(k_panel<PNL_BIG_R, PNL_BIG_NT>, n, PNL_BIG_NT, smem, s, d, k0, nleft, a0, a1);
 }
 
 // 64-deep trailing update: 64 x 64 tiles, TWO 32-deep stages through one 36 KB buffer, 128 registers -> FOUR CTAs/SM
@@ -643,8 +647,8 @@ static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk
     const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, n);
     const size_t smem = (64 * 36 + 32 * GM_LDB) * sizeof(double);
     g_rt_launches++;
-    if (K == 32) k_gemm<32, 64, 1, 4><<<g64, 128, smem, s>>>(d, i0, kk0, c0, c1, a0, a1);
-    else k_gemm<32, 64, 2, 4><<<g64, 128, smem, s>>>(d, i0, kk0, c0, c1, a0, a1);
+    if (K == 32) rt_launch(k_gemm<32, 64, 1, 4>, g64, 128, smem, s, d, i0, kk0, c0, c1, a0, a1);
+    else rt_launch(k_gemm<32, 64, 2, 4>, g64, 128, smem, s, d, i0, kk0, c0, c1, a0, a1);
 }
 
 void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
@@ -690,8 +694,8 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
                       16. * 32. * nca + 8. * (nleft_lo * ncl + nleft_hi * ncha));
         g_rt_launches++;
         const dim3 grid((c1 - c0 + TRSM_THREADS - 1) / TRSM_THREADS, ga1[g] - ga0[g]);
-        if (nleft_hi > 0) k_trsm<true><<<grid, TRSM_THREADS, trsm_smem_bytes(nleft_hi), ss>>>(d, k0, c0, c1, nleft_lo, nleft_hi, c_split, ga0[g], ga1[g]);
-        else k_trsm<false><<<grid, TRSM_THREADS, 0, ss>>>(d, k0, c0, c1, 0, 0, c_split, ga0[g], ga1[g]);
+        if (nleft_hi > 0) rt_launch(k_trsm<true>, grid, TRSM_THREADS, trsm_smem_bytes(nleft_hi), ss, d, k0, c0, c1, nleft_lo, nleft_hi, c_split, ga0[g], ga1[g]);
+        else rt_launch(k_trsm<false>, grid, TRSM_THREADS, 0, ss, d, k0, c0, c1, 0, 0, c_split, ga0[g], ga1[g]);
         rt_prof_end(m, c_trsm, ss);
     };
     auto trsm = [&](int g, int k0, int nleft_lo, int nleft_hi, int c_split) { trsm_on(st[g], g, k0, k0 + 32, ld, nleft_lo, nleft_hi, c_split); };
@@ -781,7 +785,7 @@ back_substitution:
         m->prof_layers = layers_all * (ga1[g] - ga0[g]) / std::max(bound, 1);
         rt_prof_begin(m, c_back, st[g], (double)Np * Np, 4. * Np * Np);
         g_rt_launches++;
-        k_backsolve<<<ga1[g] - ga0[g], BS_THREADS, Np * sizeof(double), st[g]>>>(d, ga0[g], ga1[g]);
+        rt_launch(k_backsolve, ga1[g] - ga0[g], BS_THREADS, Np * sizeof(double), st[g], d, ga0[g], ga1[g]);
         rt_prof_end(m, c_back, st[g]);
     }
     m->prof_layers = layers_all;
@@ -799,6 +803,7 @@ cudaError_t lu_kernels_init()
     if (const char* gp = getenv("RT_B200_PANEL_192")) g_panel_192 = atoi(gp);
     if (const char* gq = getenv("RT_B200_LU_GROUP_MIN")) g_lu_group_min = std::max(1, atoi(gq));
     if (const char* gl = getenv("RT_B200_LU_LOOKAHEAD")) g_lu_lookahead = atoi(gl);
+    if (const char* gd = getenv("RT_B200_PDL_MAX_LAYERS")) g_rt_pdl_max_layers = atoi(gd);
     const int smg = (64 * 36 + 32 * GM_LDB) * (int)sizeof(double);
     const cudaFuncAttribute at = cudaFuncAttributeMaxDynamicSharedMemorySize;
     cudaError_t e = cudaFuncSetAttribute(k_panel<1, 256>, at, 256 * 33 * (int)sizeof(double));

@@ -30,6 +30,8 @@ void launch_set_active_failed(const DevModel& d, cudaStream_t s, int b, int e);
 
 static thread_local std::string g_create_error;
 long long g_rt_launches = 0;
+thread_local int g_rt_pdl_on = 0;
+int g_rt_pdl_max_layers = 96;
 
 template <class T> static T* dev_alloc(rt_model* m, size_t n, bool cloud, bool zero = true)
 {
@@ -675,6 +677,8 @@ static rt_status solve_flagged(rt_model* m, int start_mode, int max_iter, double
     CK(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
     int it = 0;
     for (; it < max_iter && bound > 0; it++) {
+        // rt_internal.h (rt_launch): on while the batch is small enough to be latency-bound -- measured in layers of N = 768
+        g_rt_pdl_on = !m->prof_timing && (double)bound * d.Np * d.Np <= (double)g_rt_pdl_max_layers * 768. * 768.;
         enqueue_calc_new_pop(m, bound, nullptr);
         rt_prof_begin(m, c_ctl, s, 0., 8. * 6. * d.N);
         launch_ctl_step(d, s, bound, accel, max_iter, min_err);
@@ -688,6 +692,7 @@ static rt_status solve_flagged(rt_model* m, int start_mode, int max_iter, double
             m->prof_layers = bound;
         }
     }
+    g_rt_pdl_on = 0;
     CK(cudaStreamSynchronize(s));
     cudaEventDestroy(ev[0]);
     cudaEventDestroy(ev[1]);

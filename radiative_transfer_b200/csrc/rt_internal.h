@@ -121,6 +121,37 @@ struct rt_model {
 
 extern long long g_rt_launches; // every kernel launch of the library (bench.py gpu_launches)
 
+// Programmatic dependent launch for the kernels of the per-iteration chain.  An iteration with few active layers is a chain
+// of ~75 dependent kernels of 5-30 us at their latency floor; with the attribute below kernel k+1 is launched, its CTAs
+// scheduled and its preamble run while kernel k drains.  Every kernel launched through rt_launch begins with rt_pdl_sync():
+// `griddepcontrol.wait` returns when the preceding grid has completed and its writes are visible (a no-op without the
+// attribute), `griddepcontrol.launch_dependents` lets the next kernel of the stream start its own launch.  Waiting CTAs hold
+// SM slots, which costs more than it saves when another stream could use them (the grouped LU of a full batch), so the
+// driver switches it on while active layers x Np^2 <= g_rt_pdl_max_layers x 768^2 (RT_B200_PDL_MAX_LAYERS, default 96, 0 =
+// never).  Measured per iteration, N = 768: 8 layers 1.24 -> 1.13 ms, 25 layers 1.41 -> 1.34 ms, 60 layers equal, 200
+// layers 4.46 -> 4.58 ms (hence the threshold); o-H2O N = 411, 200 layers: converged solve 92.7 -> 87.8 ms.  Results are
+// bitwise unchanged (only launch timing moves).
+extern thread_local int g_rt_pdl_on;
+extern int g_rt_pdl_max_layers;
+#ifdef __CUDACC__
+static __device__ __forceinline__ void rt_pdl_sync()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+template <class... KArgs, class... Args>
+static inline void rt_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = g_rt_pdl_on ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
+
 // ---- kernel launchers (each returns after enqueueing on `s`) -------------------------------------------------
 // layers processed = active[0 .. min(*n_active, nlay_bound))
 void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int neutrals_only_half_A, int active_bound = 0);
