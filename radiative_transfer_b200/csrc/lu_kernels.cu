@@ -662,7 +662,7 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
     G = std::min(G, RT_LU_MAX_GROUPS);
     if (G > 1 && !m->lu_streams[1]) {
         for (int g = 1; g < RT_LU_MAX_GROUPS; g++) {
-            if (cudaStreamCreateWithFlags(&m->lu_streams[g], cudaStreamNonBlocking) != cudaSuccess ||
+            if (cudaStreamCreateWithPriority(&m->lu_streams[g], cudaStreamNonBlocking, m->prio_hi) != cudaSuccess ||
                 cudaEventCreateWithFlags(&m->lu_join[g], cudaEventDisableTiming) != cudaSuccess) { G = 1; break; }
         }
         if (G > 1 && cudaEventCreateWithFlags(&m->lu_fork, cudaEventDisableTiming) != cudaSuccess) G = 1;
@@ -720,7 +720,7 @@ void launch_lu_solve(rt_model* m, cudaStream_t s0, int bound)
         bool ok = true;
         for (int g = 0; g < G && ok; g++) {
             if (m->lu_side[g]) continue;
-            ok = cudaStreamCreateWithFlags(&m->lu_side[g], cudaStreamNonBlocking) == cudaSuccess;
+            ok = cudaStreamCreateWithPriority(&m->lu_side[g], cudaStreamNonBlocking, m->prio_lo) == cudaSuccess;
             for (int e = 0; e < 3 && ok; e++) ok = cudaEventCreateWithFlags(&m->lu_ev[e][g], cudaEventDisableTiming) == cudaSuccess;
         }
         if (ok) {

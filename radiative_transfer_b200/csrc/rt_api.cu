@@ -200,7 +200,13 @@ extern "C" rt_status rt_model_create(const rt_model_desc* desc, int device, rt_m
     cudaDeviceProp prop;
     cudaGetDeviceProperties(&prop, device);
     if (prop.major < 10) { g_create_error = "librt_b200 is built for sm_100a only"; delete m; return RT_ERR_CUDA; }
-    if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess) { g_create_error = "stream"; delete m; return RT_ERR_CUDA; }
+    // the critical chain of the LU (panels and what they wait for) runs on the model's stream and on the group streams, at the
+    // highest stream priority; the far-column bulk work of the look-ahead schedule runs on side streams at the lowest
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (getenv("RT_B200_NO_STREAM_PRIO")) prio_hi = prio_lo = 0;
+    m->prio_hi = prio_hi; m->prio_lo = prio_lo;
+    if (cudaStreamCreateWithPriority(&m->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess) { g_create_error = "stream"; delete m; return RT_ERR_CUDA; }
     if (cudaMallocHost((void**)&m->h_n_active, 4 * sizeof(int)) != cudaSuccess) { g_create_error = "pinned alloc"; delete m; return RT_ERR_CUDA; }
     if (cudaError_t ce = fused_kernels_init()) { g_create_error = std::string("cudaFuncSetAttribute failed: ") + cudaGetErrorString(ce); delete m; return RT_ERR_CUDA; }
     if (cudaError_t ce = lu_kernels_init()) { g_create_error = std::string("cudaFuncSetAttribute failed: ") + cudaGetErrorString(ce); delete m; return RT_ERR_CUDA; }

@@ -86,6 +86,7 @@ struct rt_model {
     size_t cloud_slot = 0;
     std::vector<std::vector<double>> h_tgrid; // host copy of the collision tables' temperature grids (set_gas_param)
     cudaStream_t stream = nullptr;
+    int prio_hi = 0, prio_lo = 0;  // stream priorities: critical chain / far-column bulk work of the look-ahead LU
     cudaStream_t lu_streams[RT_LU_MAX_GROUPS] = {};  // side streams of the grouped LU ([0] unused: group 0 runs on `stream`)
     cudaEvent_t lu_fork = nullptr, lu_join[RT_LU_MAX_GROUPS] = {};
     cudaStream_t lu_side[RT_LU_MAX_GROUPS] = {};     // look-ahead: far-column work of every group
