@@ -223,18 +223,26 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------------------------
 # this repo's arm
 # ----------------------------------------------------------------------------------------------------------------
-def run_sweep_leg(args, m, base, dist, world, rank, abi):
+def run_sweep_leg(args, m, base, dist, world, rank, abi, device):
     """Config 5 for real: G^3 DISTINCT grid points drawn from a shared queue, the per-GPU rt_model reused (tables stay
     resident), every draw = rt_cloud_upload + rt_calc_molecular_populations through host buffers.  The same G^3 points
-    run at every N (strong scaling of one sweep), so sweep.value(N) / (N sweep.value(1)) is the sweep's efficiency."""
+    run at every N (strong scaling of one sweep), so sweep.value(N) / (N sweep.value(1)) is the sweep's efficiency.
+    --sweep-workers W: W models in flight per GPU (W host threads, each with its own rt_model handle and streams, drawing
+    from the same queue; the C-ABI calls release the GIL): while one model is in the latency-bound tail of its solve (a
+    handful of active layers) the other's full-batch iterations fill the SMs -- SURVEY.md section 8e: "batch several models
+    per GPU concurrently (streams) to fill the machine"."""
     import copy
     import ctypes as C
+    import hashlib
+    import threading
     import torch
-    from radiative_transfer_b200 import sharding, synthetic
+    from radiative_transfer_b200 import sharding, solver, synthetic
     G = args.sweep_grid
     npts = G ** 3
     M = max(1, args.sweep_batch)
+    W = max(1, args.sweep_workers)
     ncomp = len(base.dust)
+    models = [m] + [solver.Model(base, device=device, upload_cloud=False) for _ in range(W - 1)]
 
     def barrier():
         if dist is not None:
@@ -243,42 +251,71 @@ def run_sweep_leg(args, m, base, dist, world, rank, abi):
 
     def run_once(tag):
         q = sharding.SweepQueue(npts, name="rt_bench_sweep_" + tag)
-        mine, busy, iters, conv, layers = [], 0.0, [], 0, 0
+        lock = threading.Lock()
+        res = dict(points=[], busy_s=0.0, iters_max_per_point=[], layers_converged=0, layers=0, digests={})
+        errs = []
+
+        def draw():
+            pts = []
+            with lock:  # one draw at a time per rank: the store round trip is atomic, the local fallback counter is not
+                for _ in range(M):
+                    try:
+                        pts.append(next(q))
+                    except StopIteration:
+                        break
+            return pts
+
+        def worker(mod):
+            try:
+                torch.cuda.set_device(device)
+                while True:
+                    pts = draw()
+                    if not pts:
+                        return
+                    t1 = time.perf_counter()
+                    probs = []
+                    for pt in pts:
+                        qq = copy.copy(base)
+                        qq.layers = synthetic.sweep_layers(pt, G, L=base.L, ncomp=ncomp)
+                        probs.append(qq)
+                    stk = probs[0] if len(probs) == 1 else sharding.stack_clouds(probs)[0]
+                    mod.cloud_upload(stk)
+                    pop = np.empty((stk.L, stk.N))
+                    stat = np.zeros(stk.L, dtype=abi.STATUS_DTYPE)
+                    mod._ck(mod.L_.rt_calc_molecular_populations(mod.h, abi.dptr(pop), abi.RT_START_BOUNDARY, int(base.accel), 150,
+                                                                 int(args.retry_cap), C.c_double(1e-5),
+                                                                 stat.ctypes.data_as(C.POINTER(abi.rt_layer_status))),
+                            "rt_calc_molecular_populations")
+                    dt = time.perf_counter() - t1
+                    with lock:
+                        res["busy_s"] += dt
+                        res["points"] += pts
+                        for k in range(len(pts)):
+                            res["iters_max_per_point"].append(int(stat["iters"][k * base.L:(k + 1) * base.L].max()))
+                            lo_, hi_ = k * base.L, (k + 1) * base.L
+                            res["digests"][int(pts[k])] = hashlib.sha256(pop[lo_:hi_].tobytes() + stat["iters"][lo_:hi_].tobytes()).hexdigest()
+                        res["layers_converged"] += int(stat["converged"].sum())
+                        res["layers"] += stk.L
+            except Exception as e:  # noqa: BLE001 -- reported by the main thread
+                errs.append(e)
+
         barrier()
         t0 = time.perf_counter()
-        while True:
-            pts = []
-            for _ in range(M):
-                try:
-                    pts.append(next(q))
-                except StopIteration:
-                    break
-            if not pts:
-                break
-            t1 = time.perf_counter()
-            probs = []
-            for pt in pts:
-                qq = copy.copy(base)
-                qq.layers = synthetic.sweep_layers(pt, G, L=base.L, ncomp=ncomp)
-                probs.append(qq)
-            stk = probs[0] if len(probs) == 1 else sharding.stack_clouds(probs)[0]
-            m.cloud_upload(stk)
-            pop = np.empty((stk.L, stk.N))
-            stat = np.zeros(stk.L, dtype=abi.STATUS_DTYPE)
-            m._ck(m.L_.rt_calc_molecular_populations(m.h, abi.dptr(pop), abi.RT_START_BOUNDARY, int(base.accel), 150, int(args.retry_cap),
-                                                     C.c_double(1e-5), stat.ctypes.data_as(C.POINTER(abi.rt_layer_status))),
-                  "rt_calc_molecular_populations")
-            busy += time.perf_counter() - t1
-            mine += pts
-            for k in range(len(pts)):
-                iters.append(int(stat["iters"][k * base.L:(k + 1) * base.L].max()))
-            conv += int(stat["converged"].sum()); layers += stk.L
-        t_end = time.perf_counter() - t0
+        ths = [threading.Thread(target=worker, args=(mod,)) for mod in models]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        res["end_s"] = time.perf_counter() - t0
+        if errs:
+            raise errs[0]
         barrier()
-        return dict(points=mine, busy_s=busy, end_s=t_end, iters_max_per_point=iters, layers_converged=conv, layers=layers)
+        return res
 
     run_once("warm") if args.sweep_warm else None
     r = run_once("timed")
+    for mod in models[1:]:
+        mod.close()
     if dist is not None:
         allr = [None] * world
         dist.all_gather_object(allr, r)
@@ -288,16 +325,23 @@ def run_sweep_leg(args, m, base, dist, world, rank, abi):
     done = sorted(sum((x["points"] for x in allr), []))
     assert done == list(range(npts)), "the queue must hand every grid point out exactly once"
     its = sum((x["iters_max_per_point"] for x in allr), [])
-    busy = [x["busy_s"] for x in allr]
+    busy = [x["busy_s"] / W for x in allr]
+    dig = {}
+    for x in allr:
+        dig.update(x["digests"])
+    # one digest over the populations + iteration counts of every grid point in point order: the answer of the sweep does not
+    # depend on how many GPUs, workers or draws produced it (layers are independent, kernels deterministic)
+    digest = hashlib.sha256("".join(dig[k] for k in sorted(dig)).encode()).hexdigest()[:16]
     return {
         "value": npts / wall, "unit": "distinct models/s", "points": npts, "grid": f"{G}x{G}x{G} (n_H2 x T x n_mol/|dv/dz|)",
-        "models_per_solve": M, "wall_s": wall, "scaling": "strong (the same %d points at every N)" % npts,
-        "per_rank": [{"points": len(x["points"]), "busy_s": round(x["busy_s"], 4), "end_s": round(x["end_s"], 4)} for x in allr],
+        "models_per_solve": M, "models_in_flight_per_gpu": W, "wall_s": wall, "answer_digest": digest, "scaling": "strong (the same %d points at every N)" % npts,
+        "per_rank": [{"points": len(x["points"]), "busy_s": round(x["busy_s"] / W, 4), "end_s": round(x["end_s"], 4)} for x in allr],
         "balance": (sum(busy) / len(busy)) / wall,
         "tail_idle_s": wall - min(x["end_s"] for x in allr),
         "iters_max_per_point": {"min": int(min(its)), "mean": float(np.mean(its)), "max": int(max(its))},
         "layers_converged": int(sum(x["layers_converged"] for x in allr)), "layers": int(sum(x["layers"] for x in allr)),
-        "schedule": "sharding.SweepQueue: atomic counter in the process group's store, %d point(s) per draw, no collective" % M,
+        "schedule": "sharding.SweepQueue: atomic counter in the process group's store, %d point(s) per draw, %d worker thread(s) "
+                    "(rt_model handles) per GPU, no collective" % (M, W),
         "timing": "host wall clock from a barrier to each rank's last result on the host; max over ranks",
     }
 
@@ -466,7 +510,7 @@ def run_gpu(args):
     # ---- config 5: the sweep of distinct models -------------------------------------------------------------------------
     sweep = None
     if args.mode == "sweep" and args.config == "ch3oh" and args.sweep_grid > 0 and args.batch == 1 and not chained:
-        sweep = run_sweep_leg(args, m, p_full, dist, world, rank, abi)
+        sweep = run_sweep_leg(args, m, p_full, dist, world, rank, abi, local)
 
     if rank != 0:
         m.close()
@@ -586,8 +630,9 @@ def main():
     ap.add_argument("--start", default="boundary", choices=["boundary", "chained"],
                     help="boundary: every layer from its own start vector, all layers at once (the measured configuration); chained: "
                          "the reference's warm-start chain, radiative_transfer.cpp:247-253 (use with --batch M)")
-    ap.add_argument("--sweep-grid", type=int, default=4, help="G: the sweep leg solves G^3 distinct grid points (0: skip the sweep leg)")
+    ap.add_argument("--sweep-grid", type=int, default=5, help="G: the sweep leg solves G^3 distinct grid points (0: skip the sweep leg)")
     ap.add_argument("--sweep-batch", type=int, default=1, help="grid points stacked into one solve per queue draw")
+    ap.add_argument("--sweep-workers", type=int, default=3, help="models in flight per GPU in the sweep leg (host threads, one rt_model each)")
     ap.add_argument("--sweep-warm", type=int, default=0, help="1: run the whole sweep once untimed first")
     ap.add_argument("--cpu-full-slab", action="store_true", help="cpu_baseline solves the WHOLE slab once instead of a sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")

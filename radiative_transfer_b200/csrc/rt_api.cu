@@ -29,7 +29,7 @@ void launch_set_active_failed(const DevModel& d, cudaStream_t s, int b, int e);
     } while (0)
 
 static thread_local std::string g_create_error;
-long long g_rt_launches = 0;
+std::atomic<long long> g_rt_launches{0};
 thread_local int g_rt_pdl_on = 0;
 int g_rt_pdl_max_layers = 96;
 
@@ -54,7 +54,12 @@ template <class T> static T* dev_upload(rt_model* m, const T* h, size_t n, bool 
 {
     T* p = dev_alloc<T>(m, n, cloud, false);
     if (p && n) {
-        if (cudaMemcpy(p, h, n * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) { m->last_error = "cudaMemcpy H2D failed"; return nullptr; }
+        // ON THE MODEL'S STREAM: a synchronous cudaMemcpy from pageable host memory returns once the data are staged -- the
+        // DMA to the device may still be in flight on the legacy stream, which a non-blocking stream does not wait for, so a
+        // kernel enqueued next on m->stream could read the previous cloud's values (seen as run-to-run differences of a sweep
+        // with several models in flight).  Stream order makes the kernels of m->stream wait for the copy; the host buffer is
+        // free again on return (pageable: staged immediately; pinned: the callers synchronise before the buffer goes away).
+        if (cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, m->stream) != cudaSuccess) { m->last_error = "cudaMemcpy H2D failed"; return nullptr; }
     }
     return p;
 }
@@ -62,13 +67,15 @@ template <class T> static T* dev_upload(rt_model* m, const T* h, size_t n, bool 
 // scratch device buffers of one entry-point call: freed on every exit path (the CK macro returns early)
 struct DevScratch {
     std::vector<void*> bufs;
+    cudaStream_t stream; // uploads are ordered on the stream whose kernels read them (see dev_upload)
+    explicit DevScratch(cudaStream_t s) : stream(s) {}
     ~DevScratch() { for (void* p : bufs) cudaFree(p); }
     void* get(size_t bytes, const void* host = nullptr)
     {
         void* p = nullptr;
         if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
         bufs.push_back(p);
-        if (host && cudaMemcpy(p, host, bytes, cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
+        if (host && cudaMemcpyAsync(p, host, bytes, cudaMemcpyHostToDevice, stream) != cudaSuccess) return nullptr;
         return p;
     }
 };
@@ -842,7 +849,7 @@ rt_status rt_calc_molecular_populations(rt_model* m, double* pop, int start_mode
                 std::vector<int> cv(L);
                 CK(cudaMemcpy(cv.data(), d.conv, sizeof(int) * L, cudaMemcpyDeviceToHost));
                 for (int l = 0; l < L; l++)
-                    if (!cv[l]) CK(cudaMemcpy(d.pop + (size_t)l * N, pop + (size_t)l * N, sizeof(double) * N, cudaMemcpyHostToDevice));
+                    if (!cv[l]) CK(cudaMemcpyAsync(d.pop + (size_t)l * N, pop + (size_t)l * N, sizeof(double) * N, cudaMemcpyHostToDevice, m->stream));
             }
             if ((r = solve_range(m, 0, L, start_mode, max_iter_ext, min_err, 0, true))) return r;
         }
@@ -900,7 +907,7 @@ rt_status rt_assemble(rt_model* m, const double* pop, double* matrix, double* df
     const int L = d.L, N = d.N, Np = d.Np;
     rt_status r = rt_set_populations(m, pop);
     if (r) return r;
-    DevScratch scratch;
+    DevScratch scratch(m->stream);
     double* df_dev = (double*)scratch.get(sizeof(double) * (size_t)L * N);
     NEED_BUF(df_dev);
     launch_set_active_range(d, m->stream, 0, L);
@@ -963,7 +970,7 @@ rt_status rt_profile_get(rt_model* m, int cap, const char** names, double* ms, l
 }
 
 long long rt_iterations_enqueued(const rt_model* m) { return m ? m->iters_enqueued : 0; }
-long long rt_launch_count(void) { return g_rt_launches; }
+long long rt_launch_count(void) { return g_rt_launches.load(); }
 
 rt_status rt_profile_get_work(rt_model* m, int cap, double* flops, double* bytes)
 {
@@ -1049,7 +1056,7 @@ extern "C" rt_status rt_intensity(rt_model* m, int lay, int up, int low, const d
     std::vector<double> buf(1 + RT_MAX_DUST, 0.);
     const std::vector<double> sg = line_sigma(m, e1);
     for (int c = 0; c < d.ncomp; c++) buf[1 + c] = sg[c];
-    DevScratch scratch;
+    DevScratch scratch(m->stream);
     double* pop_dev = (double*)scratch.get(sizeof(double) * N, pop);
     double* out_dev = (double*)scratch.get(sizeof(double) * buf.size(), buf.data());
     NEED_BUF(pop_dev && out_dev);
@@ -1093,7 +1100,7 @@ extern "C" rt_status rt_maser_postpass(rt_model* m, const double* pop, int nb_tr
     const double dv = (vmax - vmin) / (nb_freq - 1.);
     double vel = vmin;
     for (int n = 0; n < nb_freq; n++, vel += dv) vgrid[n] = vel;
-    DevScratch scratch;
+    DevScratch scratch(m->stream);
     bool ok = true;
     auto up_d = [&](const void* h, size_t bytes) { void* p = scratch.get(bytes, h); ok = ok && p; return p; };
     auto out_d = [&](size_t bytes) { void* p = scratch.get(bytes); ok = ok && p; return p; };
@@ -1146,7 +1153,7 @@ extern "C" rt_status rt_lim_luminosity(rt_model* m, const double* pop, int nb_tr
     rt_status r = rt_set_populations(m, pop);
     if (r != RT_OK) return r;
     const size_t nout = (size_t)nb_trans * L * 2;
-    DevScratch scratch;
+    DevScratch scratch(m->stream);
     int* up_dev = (int*)scratch.get(sizeof(int) * nb_trans, up);
     int* low_dev = (int*)scratch.get(sizeof(int) * nb_trans, low);
     double* out_dev = (double*)scratch.get(sizeof(double) * nout);

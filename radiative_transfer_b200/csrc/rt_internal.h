@@ -14,6 +14,7 @@
 //   hist_pop/hist_res [L][6][N]  rings of the last nb_prev_steps+1 population / residual vectors
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -120,7 +121,8 @@ struct rt_model {
     cudaEvent_t timer_ev[2] = {nullptr, nullptr};
 };
 
-extern long long g_rt_launches; // every kernel launch of the library (bench.py gpu_launches)
+extern std::atomic<long long> g_rt_launches; // every kernel launch of the library (bench.py gpu_launches); several host
+                                             // threads may drive their own rt_model handles concurrently
 
 // Programmatic dependent launch for the kernels of the per-iteration chain.  An iteration with few active layers is a chain
 // of ~75 dependent kernels of 5-30 us at their latency floor; with the attribute below kernel k+1 is launched, its CTAs

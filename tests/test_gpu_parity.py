@@ -314,6 +314,57 @@ def test_handle_survives_recoverable_errors(solver_mod, problems):
     m.close()
 
 
+def test_models_in_flight_give_the_serial_answers(solver_mod):
+    """Several rt_model handles driven concurrently from host threads (bench.py's sweep leg: models in flight per GPU), each
+    uploading DIFFERENT clouds from pageable host memory back to back: every answer is bitwise the answer of the same cloud
+    solved alone.  Regression test for uploads that were not ordered on the model's stream (a synchronous cudaMemcpy from
+    pageable memory returns when the data are staged, not when they are on the device; the next kernel on a non-blocking
+    stream could read the previous cloud's layer parameters)."""
+    import threading
+    from radiative_transfer_b200 import synthetic
+    base = synthetic.config_ch3oh(L=24, n_vt=3, n_k=8, n_j=10)  # N = 240: the multi-kernel, multi-stream path
+    clouds = [synthetic.sweep_layers(pt, 4, L=24) for pt in range(12)]
+
+    def solve(mod, lay):
+        q = copy.copy(base)
+        q.layers = lay
+        mod.cloud_upload(q)
+        pop, st = mod.calc_molecular_populations()
+        return pop, st["iters"].copy()
+
+    m0 = solver_mod.Model(base, upload_cloud=False)
+    want = [solve(m0, lay) for lay in clouds]
+    m0.close()
+    got = [None] * len(clouds)
+    nxt = iter(range(len(clouds)))
+    lock = threading.Lock()
+    errs = []
+
+    def worker():
+        try:
+            mod = solver_mod.Model(base, upload_cloud=False)
+            while True:
+                with lock:
+                    i = next(nxt, None)
+                if i is None:
+                    break
+                got[i] = solve(mod, clouds[i])
+            mod.close()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    for rep in range(2):
+        nxt = iter(range(len(clouds)))
+        ths = [threading.Thread(target=worker) for _ in range(3)]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        assert not errs, errs
+        for i, (w, g) in enumerate(zip(want, got)):
+            assert np.array_equal(w[1], g[1]) and np.array_equal(w[0], g[0]), f"cloud {i} differs when solved with other models in flight"
+
+
 # ---- BASELINE.json full sizes: size-independent properties -------------------------------------------------------
 def test_full_size_ch3oh_properties(solver_mod, best_checker):
     """Config 2 (CH3OH-A, N = 768, L = 200): normalisation, fixed-point property, layer independence, and parity
