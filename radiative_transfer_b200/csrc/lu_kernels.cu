@@ -631,7 +631,9 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
 // and the DMMA sub-pipe 74.6 % -> 64.4 % busy, profiles/r02_ncu_full_gemm_cstaged.csv): 2.91 ms -- in every
 // case the fourth resident CTA is worth more than what the variant saves; `prefetch.global.L2` of the C tile of the CTA that
 // runs 148 / 296 / 592 / 1184 block indices later (so that a tile's C loads hit L2 instead of HBM): 2.58 ms at every
-// distance against 2.53 ms without -- the update is not waiting for C.
+// distance against 2.53 ms without -- the update is not waiting for C.  The NEXT-PANEL update (32 columns) on 128 x 32 tiles
+// instead of 64 x 64 tiles of which half multiply zeros: 2.54 vs 2.55 ms for the class alone, but 4.73 vs 4.40 ms per
+// grouped full-batch iteration (half as many, twice as long CTAs on the critical chain of the look-ahead schedule): removed.
 // Layer groups of one solve (development switch RT_B200_LU_GROUPS).  The layers of a batch are independent, so the
 // active list is cut into G slices whose factorisations run on G streams: while one slice sits in a latency-bound
 // panel (one register-file-filling CTA per SM, 200 layers = 1.35 waves on 148 SMs) the trailing updates of the other
