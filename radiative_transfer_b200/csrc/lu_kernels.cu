@@ -438,9 +438,15 @@ __global__ void __launch_bounds__(TRSM_THREADS, LEFT ? TRSM_LEFT_MINB : 4) k_trs
 
 // NST stages of K columns each (kk0, kk0 + K, ...): the accumulators stay in registers across the stages, so C is read and
 // written once per NST * K eliminated columns while one stage's A / B tiles fit four CTAs per SM.
-template <int K, int ROWS, int NST, int MINB = (ROWS == 64 ? 3 : 2)>
-__global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
+// COLS = 32: the tile of the NEXT-PANEL update (32 columns wide): two warps, 64 x 32, so that no half of a 64-wide tile
+// multiplies zeros; half the threads, registers and shared memory per CTA.  With the driver's per-kernel carve-out this
+// third kernel made the grouped iteration SLOWER (4.40 -> 4.72 ms, as did a 128 x 32 tile); with the common carve-out set in
+// lu_kernels_init it is faster (4.36 -> 4.32 ms).
+template <int K, int ROWS, int NST, int MINB = (ROWS == 64 ? 3 : 2), int COLS = GM_COLS>
+__global__ void __launch_bounds__(ROWS * COLS / 32, MINB) k_gemm(DevModel d, int i0, int kk0, int c0, int c1, int a0, int a1)
 {
+    constexpr int NT = ROWS * COLS / 32;            // one warp per 32 x 32 block of the tile
+    constexpr int LDB = COLS == 64 ? GM_LDB : 36;   // row stride of the B tile, = 4 (mod 16) doubles
     rt_pdl_sync();
     const int a = a0 + blockIdx.z;
     if (a >= a1 || a >= *d.n_active) return;
@@ -452,19 +458,19 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
     double* Bs = sm + ROWS * LDA; // [K][68]
     double* __restrict__ A = d.Mmat + (size_t)lay * Np * ld;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int r0 = i0 + blockIdx.y * ROWS, cc0 = c0 + blockIdx.x * GM_COLS;
+    const int r0 = i0 + blockIdx.y * ROWS, cc0 = c0 + blockIdx.x * COLS;
     // ---- stage A (rows r0.., K columns at kk) and B (K rows at kk, 64 columns at cc0): 16-byte cp.async
     constexpr int ACH = K / 2; // 16-byte chunks per A row
     auto stage = [&](int kk) {
-        for (int e = tid; e < ROWS * ACH; e += ROWS * 2) {
+        for (int e = tid; e < ROWS * ACH; e += NT) {
             const int r = e / ACH, ch = e - r * ACH;
             double* dst = As + r * LDA + 2 * ch;
             if (r0 + r < Np) cp_async16(dst, A + (size_t)(r0 + r) * ld + kk + 2 * ch);
             else { dst[0] = 0.; dst[1] = 0.; }
         }
-        for (int e = tid; e < K * (GM_COLS / 2); e += ROWS * 2) {
-            const int q = e >> 5, ch = e & 31;
-            double* dst = Bs + q * GM_LDB + 2 * ch;
+        for (int e = tid; e < K * (COLS / 2); e += NT) {
+            const int q = e / (COLS / 2), ch = e % (COLS / 2);
+            double* dst = Bs + q * LDB + 2 * ch;
             if (cc0 + 2 * ch < c1) cp_async16(dst, A + (size_t)(kk + q) * ld + cc0 + 2 * ch);
             else { dst[0] = 0.; dst[1] = 0.; }
         }
@@ -472,7 +478,7 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
     };
     stage(kk0);
     // ---- accumulators <- C
-    const int wr = warp >> 1, wc = warp & 1;
+    const int wr = warp / (COLS / 32), wc = warp % (COLS / 32);
     const int rw = r0 + wr * 32, cw = cc0 + wc * 32;
     const int fr = lane >> 2, fc = (lane & 3) * 2;
     double acc[4][4][2];
@@ -488,7 +494,7 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
             else acc[ti][tj][0] = acc[ti][tj][1] = 0.;
         }
     const double* Aw = As + (wr * 32 + fr) * LDA + (lane & 3);
-    const double* Bw = Bs + (lane & 3) * GM_LDB + wc * 32 + fr;
+    const double* Bw = Bs + (lane & 3) * LDB + wc * 32 + fr;
 #pragma unroll 1
     for (int st = 0; st < NST; st++) {
         if (st > 0) {
@@ -503,7 +509,7 @@ __global__ void __launch_bounds__(ROWS * 2, MINB) k_gemm(DevModel d, int i0, int
 #pragma unroll
             for (int ti = 0; ti < 4; ti++) af[ti] = -Aw[ti * 8 * LDA + k4 * 4];
 #pragma unroll
-            for (int tj = 0; tj < 4; tj++) bf[tj] = Bw[k4 * 4 * GM_LDB + tj * 8];
+            for (int tj = 0; tj < 4; tj++) bf[tj] = Bw[k4 * 4 * LDB + tj * 8];
 #pragma unroll
             for (int ti = 0; ti < 4; ti++)
 #pragma unroll
@@ -638,6 +644,7 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
 // active list is cut into G slices whose factorisations run on G streams: while one slice sits in a latency-bound
 // panel (one register-file-filling CTA per SM, 200 layers = 1.35 waves on 148 SMs) the trailing updates of the other
 // slices fill the idle SMs.
+static int g_gemm32_narrow = 1; // RT_B200_GEMM32_NARROW=0: the next-panel update on 64 x 64 tiles (half of every tile idle)
 static int g_lu_groups = 2;
 static int g_lu_lookahead = 1; // development switch RT_B200_LU_LOOKAHEAD=0: every group on one stream
 static int g_lu_group_min = 48; // layers per slice below which a slice no longer fills its share of the machine: fewer groups
@@ -649,7 +656,9 @@ static void launch_gemm(const DevModel& d, cudaStream_t s, int K, int i0, int kk
     const dim3 g64((c1 - c0 + GM_COLS - 1) / GM_COLS, (d.Np - i0 + 63) / 64, n);
     const size_t smem = (64 * 36 + 32 * GM_LDB) * sizeof(double);
     g_rt_launches++;
-    if (K == 32) rt_launch(k_gemm<32, 64, 1, 4>, g64, 128, smem, s, d, i0, kk0, c0, c1, a0, a1);
+    if (K == 32 && c1 - c0 <= 32 && g_gemm32_narrow)
+        rt_launch(k_gemm<32, 64, 1, 8, 32>, g64, 64, (64 * 36 + 32 * 36) * sizeof(double), s, d, i0, kk0, c0, c1, a0, a1);
+    else if (K == 32) rt_launch(k_gemm<32, 64, 1, 4>, g64, 128, smem, s, d, i0, kk0, c0, c1, a0, a1);
     else rt_launch(k_gemm<32, 64, 2, 4>, g64, 128, smem, s, d, i0, kk0, c0, c1, a0, a1);
 }
 
@@ -801,6 +810,7 @@ int lu_max_np() { return PNL_MAXROWS; }
 
 cudaError_t lu_kernels_init()
 {
+    if (const char* gt = getenv("RT_B200_GEMM32_NARROW")) g_gemm32_narrow = atoi(gt);
     if (const char* gg = getenv("RT_B200_LU_GROUPS")) g_lu_groups = std::max(1, atoi(gg));
     if (const char* gp = getenv("RT_B200_PANEL_192")) g_panel_192 = atoi(gp);
     if (const char* gq = getenv("RT_B200_LU_GROUP_MIN")) g_lu_group_min = std::max(1, atoi(gq));
@@ -815,5 +825,29 @@ cudaError_t lu_kernels_init()
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm<true>, at, (int)trsm_smem_bytes(32));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 4>, at, smg);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 2, 4>, at, smg);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 8, 32>, at, (64 * 36 + 32 * 36) * (int)sizeof(double));
+    // ONE preferred shared-memory carve-out (70 % -> 164 KB shared, 92 KB L1) for every LU kernel: CTAs of different kernels
+    // (panels, TRSMs, updates of the two layer groups and of the side streams) follow each other on the same SM, and an SM
+    // whose resident kernels ask for different carve-outs has to drain before it re-partitions.  Measured per full-batch
+    // N = 768 iteration: driver's choice per kernel 4.40 ms; 50 % 4.62; 65-80 % 4.32; 90-100 % 4.87-4.92 (L1 too small for the
+    // TRSM gathers); 60 layers 1.95 -> 1.88 ms.  The panels of more than 164 KB get what they need regardless.
+    // RT_B200_CARVEOUT=<percent> overrides, -1 leaves the choice to the driver.
+    {
+        int pct = 70;
+        if (const char* gc = getenv("RT_B200_CARVEOUT")) pct = atoi(gc);
+        const cudaFuncAttribute ca = cudaFuncAttributePreferredSharedMemoryCarveout;
+        if (pct >= 0) {
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<1, 256>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<2, 256>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<2, 192>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_panel<PNL_BIG_R, PNL_BIG_NT>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm<true>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_trsm<false>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 4>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 2, 4>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gemm<32, 64, 1, 8, 32>, ca, pct);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_backsolve, ca, pct);
+        }
+    }
     return e;
 }
