@@ -59,6 +59,12 @@ __device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
 // pivot row; 62 us per m = 768 panel against 45 us now).  Measured alternatives, not kept: one barrier per column (each
 // warp's local winner publishes its candidate row; equal), 384 threads x 2 rows for m > 512 (equal), rows loaded straight
 // into registers instead of through the staging tile (6 % slower), 512 threads x 1 row for 256 < m <= 512 (4 % slower).
+// Round 2, measured and not kept: the SECOND panel of an outer block fused with what precedes it on the critical chain (the
+// near-column TRSM and the 32-deep next-panel update): rows loaded through the first panel's permutation, U12 by 32 threads,
+// A22 -= L21 U12 inside the staging tile on DMMA (bitwise the same factors).  It removes two kernels per outer block, but
+// serialises on ONE SM per layer work that those kernels spread over the whole GPU: 8 layers 1.13 -> 1.18 ms per
+// iteration, 200 layers 4.32 -> 4.40 ms (panel class 1.19 -> 1.52 ms, update class 2.53 -> 2.29 ms).  The same update by
+// plain FMAs on the register-resident rows was worse still (every thread reads all 8 KB of U12: +40 us per panel).
 // For 256 < m <= 384 the kernel runs as 192 threads x 2 rows: 168 registers keep TWO CTAs per SM, so 200 layers are one
 // wave instead of two (1.21 -> 1.16 ms per N = 768 slab-iteration, 0.46 -> 0.41 ms at N = 411).
 // Here the 32 columns are factored as four SUB-PANELS of 8 columns: inside a
