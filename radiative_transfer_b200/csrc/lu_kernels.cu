@@ -652,6 +652,9 @@ static void launch_panel(const DevModel& d, cudaStream_t s, int k0, int nleft, i
 // slices fill the idle SMs.
 static int g_gemm32_narrow = 1; // RT_B200_GEMM32_NARROW=0: the next-panel update on 64 x 64 tiles (half of every tile idle)
 static int g_lu_groups = 2;
+// Measured and removed (round 2): a STAGGERED start of the groups (group g starts when group g-1 leaves its first panel
+// phase, so that one group's panels would run beside the other's trailing updates): 4.34 -> 4.39 ms per full-batch
+// iteration with 2 groups, 4.41 / 4.45 ms with 3 / 4 -- the idle tail of the late group costs more than the overlap gains.
 static int g_lu_lookahead = 1; // development switch RT_B200_LU_LOOKAHEAD=0: every group on one stream
 static int g_lu_group_min = 48; // layers per slice below which a slice no longer fills its share of the machine: fewer groups
 
