@@ -194,7 +194,11 @@ typedef struct rt_layer_status {
     double eq_error, pop_error, rel_error;
 } rt_layer_status;
 
-typedef struct rt_model rt_model; /* opaque; one per host thread / GPU, no global state */
+/* Opaque handle: one molecule's tables + one resident cloud on one GPU.  No global state in the library: a handle is used by
+ * one host thread at a time; DIFFERENT handles (also on the same GPU) may be driven concurrently from different host threads
+ * -- bench.py's sweep keeps three models in flight per GPU that way (each handle owns its streams and buffers; host-to-device
+ * uploads are ordered on the handle's own stream). */
+typedef struct rt_model rt_model;
 
 void rt_params_default(rt_params* p);
 const char* rt_status_string(rt_status s);
