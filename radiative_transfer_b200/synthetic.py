@@ -403,6 +403,11 @@ def small(name: str, L: int = 6) -> Problem:
         return config_ch3oh(L=L, n_vt=3, n_k=8, n_j=10)  # N = 240
     if name == "h2o_small":
         return config_h2o(L=L, N=150, cloud_kw=H2O_THICK_CLOUD)
+    if name in ("edge33", "edge98", "edge161"):
+        # level counts at the seams of the solver's size classes: 33 (one level into the second 32-block of the register LU),
+        # 98 (just above the register-resident sizes: unpadded shared-memory LU), 161 (just above the fused kernel: blocked LU)
+        shape = {"edge33": (1, 3, 11), "edge98": (2, 7, 7), "edge161": (1, 7, 23)}[name]
+        return config_ch3oh(L=L, n_vt=shape[0], n_k=shape[1], n_j=shape[2])
     if name == "h2o_odd":
         return config_h2o(L=L, N=131)  # odd level count between the register-resident and the blocked LU sizes
     if name == "nh3":
