@@ -184,7 +184,7 @@ void launch_coll_matrix(const DevModel& d, cudaStream_t s, double* out, int half
 // hyperfine lines); writes the two radiative rates of each line
 //     yd = A_ul (1 + J)   (u -> l),   yu = A_lu J   (l -> u)          iteration_lvg.cpp:137-144
 // ------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void intensity_group(const DevModel& d, int lay, int gi, const double* __restrict__ pop)
+__device__ __forceinline__ void intensity_group(const DevModel& d, int lay, int gi, const double* __restrict__ pop, bool exact)
 {
     const LayerCtx c = dev_layer_ctx(d, lay);
     const int nb = d.grp[3 * gi], la = d.grp[3 * gi + 1];
@@ -193,7 +193,7 @@ __device__ __forceinline__ void intensity_group(const DevModel& d, int lay, int 
     double* yd = d.yd + (size_t)lay * d.R;
     double* yu = d.yu + (size_t)lay * d.R;
     if (nb == 1) {
-        const double J = dev_intensity_single(d, c, d.tr_E[la], A1ul, A1lu, pop[u1], pop[l1], d.tr_sigma + (size_t)la * d.ncomp);
+        const double J = dev_intensity_single(d, c, d.tr_E[la], A1ul, A1lu, pop[u1], pop[l1], d.tr_sigma + (size_t)la * d.ncomp, exact);
         yd[la] = A1ul * (1. + J);
         yu[la] = A1lu * J;
     }
@@ -203,7 +203,7 @@ __device__ __forceinline__ void intensity_group(const DevModel& d, int lay, int 
         const double A2ul = d.tr_Aul[lb], A2lu = d.tr_Alu[lb];
         double J1, J2;
         dev_intensity_pair(d, c, d.tr_E[la], d.grp_dxn[gi], A1ul, A1lu, A2ul, A2lu, pop[u1], pop[l1], pop[u2], pop[l2],
-                           d.tr_sigma + (size_t)la * d.ncomp, J1, J2);
+                           d.tr_sigma + (size_t)la * d.ncomp, J1, J2, exact);
         yd[la] = A1ul * (1. + J1);
         yu[la] = A1lu * J1;
         yd[lb] = A2ul * (1. + J2);
@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(128) k_intensity(DevModel d, int nlay_bound)
     const int lay = d.active[a];
     const int gi = blockIdx.x * blockDim.x + threadIdx.x;
     if (gi >= d.G) return;
-    intensity_group(d, lay, gi, d.pop + (size_t)lay * d.N);
+    intensity_group(d, lay, gi, d.pop + (size_t)lay * d.N, false); // the iteration: physics.cuh, dev_intensity_single
 }
 
 // every layer (no active list), populations from pop + lay * pop_stride (stride 0: the same vector for all layers)
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(128) k_intensity_all(DevModel d, const double*
     const int lay = blockIdx.y;
     const int gi = blockIdx.x * blockDim.x + threadIdx.x;
     if (gi >= d.G) return;
-    intensity_group(d, lay, gi, pop + (size_t)lay * pop_stride);
+    intensity_group(d, lay, gi, pop + (size_t)lay * pop_stride, true); // one-shot evaluation for lim_luminosity_lvg
 }
 
 void launch_intensity(const DevModel& d, cudaStream_t s, int nlay_bound)
@@ -265,8 +265,11 @@ __global__ void __launch_bounds__(128) k_loss_rates(DevModel d, const double* __
             if (i == j) continue;
             const double Aij = d.einst[(size_t)i * N + j], Aji = d.einst[(size_t)j * N + i];
             if (Aij != 0. && i != lo && i != hi) {
-                const bool down = i < j && p[i] * Aij > p[j] * Aji;
-                const bool upw = i > j && p[i] * Aij < p[j] * Aji;
+                // the reference compares the two ROUNDED products (maser_luminosity.cpp:53,57): no contraction into
+                // fma(p_i, A_ij, -(p_j A_ji)) > 0, which decides differently when the pair is within rounding of balance
+                const double lhs = __dmul_rn(p[i], Aij), rhs = __dmul_rn(p[j], Aji);
+                const bool down = i < j && lhs > rhs;
+                const bool upw = i > j && lhs < rhs;
                 if (down || upw) {
                     double rate = down ? Aji : 0.; // J = 0 when the pair is not a line of the scheme
                     for (int e = d.row_ptr[j]; e < d.row_ptr[j + 1]; e++)

@@ -12,11 +12,12 @@ __global__ void k_intensity_single(DevModel d, int lay, int u1, int l1, double A
     // else passed through out[1..ncomp] by the host
     for (int k = 0; k < d.ncomp; k++) sigma[k] = out[1 + k];
     const double e1 = d.energy[u1] - d.energy[l1];
-    if (which == 0) out[0] = dev_intensity_single(d, c, e1, A1ul, A1lu, pop[u1], pop[l1], sigma);
+    // one-shot evaluation: the reference's operation order exactly (physics.cuh, dev_intensity_single `exact`)
+    if (which == 0) out[0] = dev_intensity_single(d, c, e1, A1ul, A1lu, pop[u1], pop[l1], sigma, true);
     else {
         double J1, J2;
         const double dxn = (d.energy[u1] - d.energy[l1] - d.energy[u2] + d.energy[l2]) * d.prm.speed_of_light;
-        dev_intensity_pair(d, c, e1, dxn, A1ul, A1lu, A2ul, A2lu, pop[u1], pop[l1], pop[u2], pop[l2], sigma, J1, J2);
+        dev_intensity_pair(d, c, e1, dxn, A1ul, A1lu, A2ul, A2lu, pop[u1], pop[l1], pop[u2], pop[l2], sigma, J1, J2, true);
         out[0] = which == 1 ? J1 : J2;
     }
 }

@@ -131,12 +131,22 @@ __device__ __forceinline__ double dev_dust_opacity(const DevModel& d, const Laye
 }
 
 // iteration_scheme_lvg::intensity_calc, iteration_lvg.cpp:163-185
+// `exact`: the net absorption as the difference of two ROUNDED products, operation by operation as the reference's expression
+// evaluates without FMA hardware (iteration_lvg.cpp:171-172).  The two forms differ by the rounding of one product, which is
+// the whole answer for a line AT the inversion threshold (absorption = stimulated emission: J = S ep reaches 1e8 and moves by
+// 1e-5 relative; seen at BASELINE size in lim_luminosity_lvg).  The one-shot evaluations (rt_intensity, rt_lim_luminosity)
+// use the exact form.  The ITERATION keeps the contracted form on purpose: the difference of rounded products can cancel to
+// exactly 0, leaving line_opacity = MIN_LINE_OPACITY = 1e-99 and J ~ 1e80 -- the un-contracted iteration walked two of the
+// rounding-sensitive layers of the BASELINE slabs into such states (negative populations flagged as converged; a next step
+// with eq_error 1e53); the fused multiply-subtract leaves the product's rounding residual instead and stays finite.
 __device__ __forceinline__ double dev_intensity_single(const DevModel& d, const DevLvg& lvg, const LayerCtx& c, double energy,
-                                                       double Aul, double Alu, double n_u, double n_l, const double* sigma)
+                                                       double Aul, double Alu, double n_u, double n_l, const double* sigma,
+                                                       bool exact = false)
 {
     const double cc = c.mol_conc / (d.prm.eight_pi * c.vel_width * energy * energy * energy);
     const double line_emiss = cc * Aul * n_u;
-    double line_opacity = cc * Alu * n_l - line_emiss + d.prm.min_line_opacity;
+    double line_opacity = exact ? __dadd_rn(__dsub_rn(__dmul_rn(__dmul_rn(cc, Alu), n_l), line_emiss), d.prm.min_line_opacity)
+                                : cc * Alu * n_l - line_emiss + d.prm.min_line_opacity;
     if (line_opacity < 0.) line_opacity *= d.prm.inv_trans_factor;
     const double dust_opacity = dev_dust_opacity(d, c, sigma);
     const double avg = fabs(c.vel_grad);
@@ -146,9 +156,9 @@ __device__ __forceinline__ double dev_intensity_single(const DevModel& d, const 
     return line_emiss / line_opacity * ep1;
 }
 __device__ __forceinline__ double dev_intensity_single(const DevModel& d, const LayerCtx& c, double energy, double Aul,
-                                                       double Alu, double n_u, double n_l, const double* sigma)
+                                                       double Alu, double n_u, double n_l, const double* sigma, bool exact = false)
 {
-    return dev_intensity_single(d, d.lvg, c, energy, Aul, Alu, n_u, n_l, sigma);
+    return dev_intensity_single(d, d.lvg, c, energy, Aul, Alu, n_u, n_l, sigma, exact);
 }
 
 // iteration_scheme_line_overlap::intensity_calc(u1,l1,u2,l2,...), iteration_lvg.cpp:428-501.
@@ -156,14 +166,16 @@ __device__ __forceinline__ double dev_intensity_single(const DevModel& d, const 
 __device__ __forceinline__ void dev_intensity_pair(const DevModel& d, const LayerCtx& c, double energy1, double dx_num,
                                                    double A1ul, double A1lu, double A2ul, double A2lu, double n_u1,
                                                    double n_l1, double n_u2, double n_l2, const double* sigma1,
-                                                   double& intens1, double& intens2)
+                                                   double& intens1, double& intens2, bool exact = false)
 {
     const double max_dx = d.prm.max_dx;
     double cc = c.mol_conc / (d.prm.eight_pi * c.vel_width * energy1 * energy1 * energy1);
     const double line_emiss1 = cc * A1ul * n_u1;
-    double line_opacity1 = cc * (A1lu * n_l1 - A1ul * n_u1) + d.prm.min_line_opacity;
+    double line_opacity1 = exact ? __dadd_rn(__dmul_rn(cc, __dsub_rn(__dmul_rn(A1lu, n_l1), __dmul_rn(A1ul, n_u1))), d.prm.min_line_opacity)
+                                 : cc * (A1lu * n_l1 - A1ul * n_u1) + d.prm.min_line_opacity;
     const double line_emiss2 = cc * A2ul * n_u2;
-    double line_opacity2 = cc * (A2lu * n_l2 - A2ul * n_u2) + d.prm.min_line_opacity;
+    double line_opacity2 = exact ? __dadd_rn(__dmul_rn(cc, __dsub_rn(__dmul_rn(A2lu, n_l2), __dmul_rn(A2ul, n_u2))), d.prm.min_line_opacity)
+                                 : cc * (A2lu * n_l2 - A2ul * n_u2) + d.prm.min_line_opacity;
     if (line_opacity1 < 0.) line_opacity1 *= d.prm.inv_trans_factor;
     if (line_opacity2 < 0.) line_opacity2 *= d.prm.inv_trans_factor;
     const double avg = fabs(c.vel_grad);
