@@ -81,3 +81,34 @@ def test_full_slab_maser_postpass_and_luminosity(case):
     want_l = chk.lim_luminosity(p, pop, up, low, beaming_factor=1.0, lay_nb_hg=want["scalars"][:, 4])
     for k in ("lum_arr", "pump_eff_arr", "loss_rate_arr", "pump_rate_arr", "emiss_coeff_arr", "exc_temp_arr", "lum", "tau_sat", "temp_sat"):
         assert np.allclose(lim[k], want_l[k], rtol=1e-9, atol=0.0, equal_nan=True), k
+
+
+@pytest.mark.parametrize("case,stride", [("oh", 1), ("oh_overlap", 4), ("h2o150", 2), ("h2o", 5), ("ch3oh", 8)])
+def test_full_slab_one_step_from_reference_populations(case, stride):
+    """One calc_new_pop (iteration_lvg.cpp:87-110: intensities, assembly, dense solve) at BASELINE size from the REFERENCE's
+    converged populations, every `stride`-th layer, CUDA path against the checker on the same input: new populations within
+    1e-6 (levels above 1e-30) and eq_error within 1e-6 relative (+1e-11, its rounding floor) on every layer that is not rounding-sensitive by the fixture's
+    own measurement -- the one-step counterpart of the converged-solve test, free of the iteration's amplification."""
+    import torch
+    assert torch.cuda.is_available(), "the gpu-marked tests need a CUDA device"
+    from oracle.loader import Checker, ref_available
+    from radiative_transfer_b200 import solver
+    p = F.problem(case)
+    gold = F.load(case)
+    sens = F.sensitive(gold)
+    idx = [l for l in range(0, p.L, stride) if np.isfinite(gold["pop"][l]).all() and not sens[l] and l not in F.ALLOW.get(case, {})]
+    assert len(idx) >= 20
+    q = p.take(idx)
+    pop = np.ascontiguousarray(gold["pop"][idx])
+    chk = Checker("ref" if ref_available() else "port")
+    want, eq_w = chk.step(q, pop)
+    m = solver.Model(q)
+    got, eq_g = m.calc_new_pop(pop)
+    m.close()
+    assert np.allclose(got.sum(axis=1), 1.0, atol=1e-9)
+    for k, l in enumerate(idx):
+        big = want[k] > 1e-30
+        err = float(np.max(np.abs(got[k] - want[k])[big] / want[k][big]))
+        assert err < 1e-6, (case, l, err)
+        # eq_error = max |e0 - M pop| is a residual AT convergence: rounding of row sums of O(1e3) rates sets its floor
+        assert abs(eq_g[k] - eq_w[k]) <= 1e-6 * eq_w[k] + 1e-11, (case, l, eq_g[k], eq_w[k])
