@@ -104,8 +104,14 @@ def test_full_slab_one_step_from_reference_populations(case, stride):
     want, eq_w = chk.step(q, pop)
     m = solver.Model(q)
     got, eq_g = m.calc_new_pop(pop)
+    bnd = m.boundary_layer_populations()
     m.close()
     assert np.allclose(got.sum(axis=1), 1.0, atol=1e-9)
+    # boundary_layer_populations (iteration_control.cpp:52-91) of the same layers: the start vectors of the measured mode
+    bnd_w = chk.boundary(q)
+    for k, l in enumerate(idx):
+        big = bnd_w[k] > 1e-30
+        assert float(np.max(np.abs(bnd[k] - bnd_w[k])[big] / bnd_w[k][big])) < 1e-7, (case, l, "boundary")
     for k, l in enumerate(idx):
         big = want[k] > 1e-30
         err = float(np.max(np.abs(got[k] - want[k])[big] / want[k][big]))
