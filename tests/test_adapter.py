@@ -53,6 +53,31 @@ def test_reference_objects_through_adapter_on_gpu(adapter, ref, problems, name, 
     assert rel_err(pop[solid], pop_o[solid], 1e-30) < 1e-6
 
 
+@pytest.mark.gpu
+def test_adapter_default_call_at_full_level_count(adapter):
+    """The drop-in as a maintainer would call it -- calc_molecular_populations_gpu with the reference's OWN objects
+    (energy_diagram, einstein_coeff, collisional_transitions, cloud_data, iteration_scheme_lvg built by the harness from the
+    flat problem) and its DEFAULT start mode, the reference's warm-start chain -- on the headline molecule (N = 768, 40
+    layers), against the committed answer of the reference's calc_molecular_populations (fixture ch3oh_chained): every layer,
+    with the same rules as tests/test_gpu_full_slab.py."""
+    import full_slab_cases as F
+    import golden_cases as G
+    from radiative_transfer_b200 import abi
+    p = F.problem("ch3oh_chained")
+    gold = F.load("ch3oh_chained")
+    assert G.problem_digest(p) == bytes(gold["digest"]).decode()
+    d, h1 = p.desc()
+    s, h2 = p.layer_soa()
+    pop = np.zeros((p.L, p.N))
+    st = np.zeros(p.L, dtype=abi.STATUS_DTYPE)
+    rc = adapter.ref_adapter_calc_molecular_populations(C.byref(d), C.byref(s), abi.dptr(pop), int(p.accel), abi.RT_START_CHAINED, 0,
+                                                        st.ctypes.data_as(C.POINTER(abi.rt_layer_status)))
+    assert rc == 0
+    rep, fails = F.compare(p, pop, st, gold, F.ALLOW.get("ch3oh_chained", {}))
+    assert not fails, fails[:10]
+    assert rep["flags_equal"] == p.L
+
+
 # ---- rt_b200::scheme_gpu: the per-call drop-in (a scheme object whose step runs on the GPU) ----------------------------
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ["ch3oh_small", "oh_overlap", "generic"])
