@@ -323,7 +323,99 @@ __device__ __forceinline__ void fused_lu_regs(double* M, int ldm, short* s_row, 
     __syncthreads();
 }
 
-// LUV: 1..3 = register-resident LU with NQ = LUV (Np = 32 LUV), 0 = LU in shared memory (any Np <= 160).  One kernel per
+// ------------------------------------------------------------------------------------------------------------------
+// The same register-resident LU for a dimension n that is NOT a multiple of 32 (96 < n <= 32 NQ, the unpadded matrices of
+// fused_dim: o-H2O at the reference driver's N = 150).  Differences: the right-hand side is column n of the matrix and rides
+// in the slot of the warp that owns that column (no per-warp copy: the registers are needed for the 5 x 19 matrix entries
+// per thread), rows >= n are marked as used from the start and never loaded or stored, a block runs min(8, n - 8 KB) steps,
+// and NS = n / 8 + 1 slots cover the columns 0 .. n.
+// ------------------------------------------------------------------------------------------------------------------
+template <int NQ, int NS, int KB>
+__device__ __forceinline__ void regn_lu_block(double (&a)[NQ][NS], unsigned& done, double* M, int ldm, int n, short* s_row, double* s_l,
+                                              int (*s_pv)[4], int w, int lane)
+{
+    constexpr int Np = 32 * NQ, NACT = NS - KB;
+    if (8 * KB > n) return; // uniform: column n (the right-hand side) was the last one
+    const int nsteps = n - 8 * KB < 8 ? n - 8 * KB : 8;
+    for (int kk = 0; kk < nsteps; kk++) {
+        const int k = 8 * KB + kk, par = k & 1;
+        const int p = s_pv[par][0];
+        double l[NQ];
+#pragma unroll
+        for (int i = 0; i < NQ; i++) {
+            l[i] = s_l[par * Np + lane + 32 * i];
+            done |= (unsigned)(lane + 32 * i == p) << i;
+        }
+        const int ph = p >> 5, pl = p & 31;
+        {
+            double col[NQ];
+#pragma unroll
+            for (int i = 0; i < NQ; i++) col[i] = a[i][0];
+            const double u = __shfl_sync(0xffffffffu, sel_row<NQ>(col, ph), pl);
+            if (w > kk) {
+#pragma unroll
+                for (int i = 0; i < NQ; i++) a[i][0] -= l[i] * u;
+            }
+        }
+        if (NACT > 1) reg_update<NQ, NS, 1, (NACT > 1 ? 2 : 1)>(a, l, ph, pl);
+        if (k + 1 < n && w == ((kk + 1) & 7)) {
+            double v[NQ];
+#pragma unroll
+            for (int i = 0; i < NQ; i++) v[i] = (kk == 7 && NACT > 1) ? a[i][NACT > 1 ? 1 : 0] : a[i][0];
+            reg_pivot<NQ>(v, done, k + 1, lane, s_l + (par ^ 1) * Np, s_pv[par ^ 1], s_row);
+        }
+        if (NACT > 2) reg_update<NQ, NS, 2, NACT>(a, l, ph, pl);
+        __syncthreads();
+    }
+    if (w + 8 * KB <= n) {
+#pragma unroll
+        for (int i = 0; i < NQ; i++)
+            if (lane + 32 * i < n) M[(size_t)(lane + 32 * i) * ldm + w + 8 * KB] = a[i][0];
+    }
+#pragma unroll
+    for (int i = 0; i < NQ; i++) {
+#pragma unroll
+        for (int j = 0; j + 1 < NACT; j++) a[i][j] = a[i][j + 1];
+    }
+}
+template <int NQ, int NS, int KB> struct RegnLuBlocks {
+    static __device__ __forceinline__ void run(double (&a)[NQ][NS], unsigned& done, double* M, int ldm, int n, short* s_row, double* s_l,
+                                               int (*s_pv)[4], int w, int lane)
+    {
+        regn_lu_block<NQ, NS, KB>(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
+        RegnLuBlocks<NQ, NS, KB + 1>::run(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
+    }
+};
+template <int NQ, int NS> struct RegnLuBlocks<NQ, NS, NS> {
+    static __device__ __forceinline__ void run(double (&)[NQ][NS], unsigned&, double*, int, int, short*, double*, int (*)[4], int, int) {}
+};
+// n <= 8 NS - 1 and n <= 32 NQ (checked by the launcher).  All FUSED_THREADS threads call it; ends with a barrier.
+template <int NQ, int NS>
+__device__ __forceinline__ void fused_lu_regs_n(double* M, int ldm, int n, short* s_row, double* s_l, int (*s_pv)[4], int w, int lane)
+{
+    double a[NQ][NS];
+    unsigned done = 0u;
+#pragma unroll
+    for (int i = 0; i < NQ; i++) {
+        const int row = lane + 32 * i;
+        const double* Mr = M + (size_t)row * ldm;
+        done |= (unsigned)(row >= n) << i;
+#pragma unroll
+        for (int j = 0; j < NS; j++) a[i][j] = (row < n && w + 8 * j <= n) ? Mr[w + 8 * j] : 0.;
+    }
+    if (w == 0) {
+        double v[NQ];
+#pragma unroll
+        for (int i = 0; i < NQ; i++) v[i] = a[i][0];
+        reg_pivot<NQ>(v, done, 0, lane, s_l, s_pv[0], s_row);
+    }
+    __syncthreads();
+    RegnLuBlocks<NQ, NS, 0>::run(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
+    __syncthreads();
+}
+
+// LUV: 1..3 = register-resident LU with NQ = LUV (Np = 32 LUV), 4..5 = the same for an unpadded dimension (NQ = LUV,
+// 96 < n <= 128 and 128 < n <= 151), 0 = LU in shared memory (any Np <= 160).  One kernel per
 // variant so that the register allocation of the small, common sizes (two CTAs per SM) is not set by the large ones.
 // CS: molecule constants staged in shared memory (false: the matrix needs the room; they are read through L1/L2).
 template <int LUV, bool CS = true>
@@ -528,7 +620,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         //    (packed 64-bit keys, two REDUX max), interchanges the two positions and computes 1/pivot;
         //  * warps 1-7 apply step k to columns k+2 .. Np (rhs) as a 14 x 16 thread grid.
         // Values that agree in their top 56 bits count as ties (relative difference < 3e-14: immaterial for the pivot).
-        if constexpr (LUV > 0) fused_lu_regs<LUV>(M, ldm, s_row, s_l, s_pv, warp, lane); // Np = 64: OH, NH3, H2CO
+        if constexpr (LUV >= 4) fused_lu_regs_n<LUV, LUV == 4 ? 17 : 19>(M, ldm, Np, s_row, s_l, s_pv, warp, lane); // o-H2O N = 150
+        else if constexpr (LUV > 0) fused_lu_regs<LUV>(M, ldm, s_row, s_l, s_pv, warp, lane); // Np = 64: OH, NH3, H2CO
         else {
             for (int r = tid; r < Np; r += FUSED_THREADS) s_row[r] = (short)r;
             __syncthreads();
@@ -575,7 +668,7 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
             }
         }
         if (warp == 0) {
-            if constexpr (LUV > 0) fused_backsolve<LUV>(M, ldm, Np, s_row, gnew, lane);
+            if constexpr (LUV > 0 && LUV <= 3) fused_backsolve<LUV>(M, ldm, Np, s_row, gnew, lane);
             else if (Np <= 128) fused_backsolve_n<4>(M, ldm, Np, s_row, gnew, lane);
             else fused_backsolve_n<5>(M, ldm, Np, s_row, gnew, lane);
         }
@@ -586,6 +679,9 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     }
 }
 
+// RT_B200_FUSED_SHARED_LU=1: the shared-memory LU for every Np > 96 (the round-2 path, kept for A/B measurements and as the
+// path of 151 < n <= 158)
+static int g_fused_shared_lu = 0;
 static bool fused_fits(const DevModel& d, bool cs) { return fused_smem_doubles(d, cs) * sizeof(double) <= FUSED_DYN_SMEM_MAX; }
 
 void launch_fused_solve(const DevModel& d, cudaStream_t s, int nlay, int accel, int max_iter, double min_err)
@@ -597,9 +693,15 @@ void launch_fused_solve(const DevModel& d, cudaStream_t s, int nlay, int accel, 
     case 32: k_fused_solve<1><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
     case 64: k_fused_solve<2><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
     case 96: k_fused_solve<3><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
-    default:
-        if (cs) k_fused_solve<0, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+    default: {
+        const int n = fused_dim(d), v = g_fused_shared_lu ? 0 : n <= 128 ? 4 : n <= 151 ? 5 : 0;
+        if (v == 4 && cs) k_fused_solve<4, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        else if (v == 4) k_fused_solve<4, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        else if (v == 5 && cs) k_fused_solve<5, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        else if (v == 5) k_fused_solve<5, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        else if (cs) k_fused_solve<0, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
         else k_fused_solve<0, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+    }
     }
 }
 
@@ -625,5 +727,11 @@ cudaError_t fused_kernels_init()
     if (e == cudaSuccess) e = fused_set_smem<1, true>();
     if (e == cudaSuccess) e = fused_set_smem<2, true>();
     if (e == cudaSuccess) e = fused_set_smem<3, true>();
+    if (e == cudaSuccess) e = fused_set_smem<4, true>();
+    if (e == cudaSuccess) e = fused_set_smem<4, false>();
+    if (e == cudaSuccess) e = fused_set_smem<5, true>();
+    if (e == cudaSuccess) e = fused_set_smem<5, false>();
+    const char* v = getenv("RT_B200_FUSED_SHARED_LU");
+    g_fused_shared_lu = v && atoi(v) != 0;
     return e;
 }
