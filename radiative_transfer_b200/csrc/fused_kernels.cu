@@ -31,11 +31,13 @@ __host__ __device__ inline size_t fused_const_doubles(const DevModel& d)
     const size_t halves = d.scheme == RT_SCHEME_LINE_OVERLAP ? 6 * G : 0;
     return 3 * R + R * (d.ncomp > 0 ? d.ncomp : 1) + G + axes + halves + (ints + 1) / 2 + 2;
 }
-// Dimension of the matrix the CTA factors.  The register-resident LU (Np <= 96) works on whole 32-row slots like the
-// blocked multi-kernel LU; above that the matrix is NOT padded to a multiple of 32 (N = 150: 181 KB instead of 206 KB, the
-// difference between fitting and not fitting): N, rounded up to an even number so that the row stride N + 1 stays odd
-// (conflict-free column walks); an odd N gets one identity row / column, which is what Cmat holds there anyway.
-__host__ __device__ inline int fused_dim(const DevModel& d) { return d.Np <= 96 ? d.Np : ((d.N + 1) & ~1); }
+// Dimension of the matrix the CTA factors: N, NOT padded to a multiple of 32 (N = 150: 181 KB instead of 206 KB, the
+// difference between fitting and not fitting; OH N = 56: 56 pivot steps instead of 64), rounded up to an even number so that
+// the row stride N + 1 stays odd (conflict-free column walks); an odd N gets one identity row / column, which is what Cmat
+// holds there anyway.
+// (written as N + (N & 1): with (N + 1) & ~1 the compiler proves n even and the register LU of NQ >= 4, which sits at the
+// 255-register limit, comes out with 0.3 - 1.9 KB of spills)
+__host__ __device__ inline int fused_dim(const DevModel& d) { return d.N + (d.N & 1); }
 // cs: molecule constants staged in shared memory (small molecules); otherwise read through L1/L2 every iteration
 __host__ __device__ inline size_t fused_smem_doubles(const DevModel& d, bool cs)
 {
@@ -68,38 +70,10 @@ __device__ __forceinline__ unsigned long long pivot_key(double v, int off)
     return ((unsigned long long)__double_as_longlong(fabs(v)) & ~0xFFull) | (unsigned long long)(0xFF - off);
 }
 
-// back substitution by one warp, NQ = Np / 32 position slots per lane, right-looking, no barriers
+// back substitution by one warp, NQ position slots per lane (n <= 32 NQ: lanes beyond n idle along), right-looking, no
+// barriers
 template <int NQ>
-__device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int Np, const short* rowf, double* gnew, int lane)
-{
-    double b[NQ], rd[NQ];
-    const double* rowp[NQ];
-#pragma unroll
-    for (int q = 0; q < NQ; q++) {
-        const int r = lane + 32 * q;
-        rowp[q] = M + (size_t)rowf[r] * ldm;
-        b[q] = rowp[q][Np];
-        rd[q] = __drcp_rn(rowp[q][r]);
-    }
-#pragma unroll
-    for (int qi = NQ - 1; qi >= 0; qi--) {
-#pragma unroll 8
-        for (int ii = 31; ii >= 0; ii--) {
-            const int i = 32 * qi + ii;
-            const double xi = __shfl_sync(0xffffffffu, b[qi] * rd[qi], ii);
-#pragma unroll
-            for (int q = 0; q < qi; q++) b[q] -= rowp[q][i] * xi;
-            if (lane < ii) b[qi] -= rowp[qi][i] * xi;
-            else if (lane == ii) b[qi] = xi;
-        }
-    }
-#pragma unroll
-    for (int q = 0; q < NQ; q++) gnew[lane + 32 * q] = b[q];
-}
-
-// the same for a dimension n that is not a multiple of 32 (n <= 32 NQ): lanes beyond n idle along
-template <int NQ>
-__device__ __forceinline__ void fused_backsolve_n(const double* M, int ldm, int n, const short* rowf, double* gnew, int lane)
+__device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int n, const short* rowf, double* gnew, int lane)
 {
     double b[NQ], rd[NQ];
     const double* rowp[NQ];
@@ -130,18 +104,19 @@ __device__ __forceinline__ void fused_backsolve_n(const double* M, int ldm, int 
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// Register-resident LU for Np = 32 * NQ <= 96 (OH N = 56, NH3, H2CO: Np = 64).  The matrix lives in the registers of the
-// CTA's 8 warps for the whole factorisation:
-//   warp w owns the columns c == w (mod 8)  (NS = Np / 8 column slots per thread, slot j <-> column w + 8 j),
-//   lane l owns the rows  l, l + 32, ...     (NQ rows per thread);  the right-hand side rides in b[NQ] (warp 0's is real).
+// Register-resident LU for every dimension n = fused_dim <= 150 (n <= 32 NQ rows, NS = n / 8 + 1 column slots; OH N = 56,
+// NH3, H2CO: NQ = 2; o-H2O at the reference driver's N = 150: NQ = 5).  The matrix lives in the registers of the CTA's 8
+// warps for the whole factorisation:
+//   warp w owns the columns c == w (mod 8)  (slot j <-> column w + 8 j; column n is the right-hand side),
+//   lane l owns the rows  l, l + 32, ...     (NQ rows per thread; rows >= n are marked as used and never loaded or stored).
 // Step k:  every warp gets the pivot row's values of ITS columns with one shuffle per slot (the pivot row is a lane, not
-// memory), the multipliers l_i = a[i][k] / pivot come from a 2 x Np double-buffered shared array written by the warp that
+// memory), the multipliers l_i = a[i][k] / pivot come from a 2 x 32 NQ double-buffered shared array written by the warp that
 // owns column k -- that warp ran one column AHEAD during step k-1 (updated column k first, REDUX arg-max on packed keys,
 // drcp, multipliers), so the CTA needs ONE barrier per column and no shared-memory traffic for the matrix itself.
-// Rows never move: pos[] is each row's position in the reference's row order (interchange k <-> p swaps two positions), it
-// gives the candidates (pos > k), the tie-break (smallest position) and, at the end, the row order of U.
+// Rows never move: a used-row mask gives the candidates, s_row[k] = pivot row of step k the row order of U at the end.
 // Column slots are processed in blocks of 8 columns (one per warp); a finished block is stored to shared memory (U for the
-// back substitution) and the slots shift down, so the step body is the same code for every k of a block.
+// back substitution) and the slots shift down, so the step body is the same code for every k of a block; a block runs
+// min(8, n - 8 KB) steps.
 // ------------------------------------------------------------------------------------------------------------------
 template <int NQ> __device__ __forceinline__ double sel_row(const double (&v)[NQ], int h)
 {
@@ -221,117 +196,20 @@ __device__ __forceinline__ void reg_update(double (&a)[NQ][NS], const double (&l
     }
 }
 
-// Steps 8 KB .. 8 KB + 7, one CTA barrier per step; the publications (multipliers + pivot row) are double-buffered by
-// column parity.  Measured alternatives, all slower or equal on B200 (OH N = 56, per iteration): warps decoupled through
+// Steps 8 KB .. 8 KB + 7 (fewer in the last block), one CTA barrier per step; the publications (multipliers + pivot row)
+// are double-buffered by column parity.  Measured alternatives, all slower or equal on B200 (OH N = 56, per iteration): warps decoupled through
 // per-step mbarriers so that the rank-1 updates trail behind the pivot chain: 30 us vs 31 us; spinning on a shared-memory
 // counter instead of mbarriers: 155 us; speculative reciprocals of every lane's candidate: slower; columns BLOCKED by warps
 // (warp w owns 8 consecutive columns and factors its sub-panel alone, warp-synchronously; the others apply the 8 pivots after
 // ONE barrier: 8 barriers per factorisation instead of 64, bitwise the same factors): 71.1 vs 72.0 ms per OH solve, i.e.
 // equal -- ncu then shows the owner warp's factorisation alone covering 74 % of the wall time at ~180 instructions and
 // ~700 cycles per column.  The step is bound by the instruction count of the warp that searches the pivot (~3-4 cycles per
-// dependent instruction of a single warp), not by the barrier.
+// dependent instruction of a single warp), not by the barrier.  The same two questions asked again at N = 150 (NQ = 5, 19
+// slots, where the rank-1 updates are 10 x the work): publications through an 8-deep ring guarded by full / empty mbarriers
+// instead of the CTA barrier: 18.4 vs 18.6 ms per solve; a warp-uniform switch on the pivot row's slot instead of the 5-way
+// select per column slot (a third of the step's instructions): 18.5 vs 18.6 ms -- equal, not kept.
 template <int NQ, int NS, int KB>
-__device__ __forceinline__ void reg_lu_block(double (&a)[NQ][NS], double (&b)[NQ], unsigned& done, double* M, int ldm, short* s_row,
-                                             double* s_l, int (*s_pv)[4], int w, int lane)
-{
-    constexpr int Np = 32 * NQ, NACT = NS - KB;
-    for (int kk = 0; kk < 8; kk++) {
-        const int k = 8 * KB + kk, par = k & 1;
-        const int p = s_pv[par][0];
-        double l[NQ];
-#pragma unroll
-        for (int i = 0; i < NQ; i++) {
-            l[i] = s_l[par * Np + lane + 32 * i];
-            done |= (unsigned)(lane + 32 * i == p) << i;
-        }
-        const int ph = p >> 5, pl = p & 31;
-        // slot 0 holds column w + 8 KB: already eliminated for w <= kk
-        {
-            double col[NQ];
-#pragma unroll
-            for (int i = 0; i < NQ; i++) col[i] = a[i][0];
-            const double u = __shfl_sync(0xffffffffu, sel_row<NQ>(col, ph), pl);
-            if (w > kk) {
-#pragma unroll
-                for (int i = 0; i < NQ; i++) a[i][0] -= l[i] * u;
-            }
-        }
-        if (NACT > 1) reg_update<NQ, NS, 1, (NACT > 1 ? 2 : 1)>(a, l, ph, pl);
-        // look-ahead: the owner of column k + 1 finds its pivot and publishes the multipliers for the next step
-        if (k + 1 < Np && w == ((kk + 1) & 7)) {
-            double v[NQ];
-#pragma unroll
-            for (int i = 0; i < NQ; i++) v[i] = (kk == 7 && NACT > 1) ? a[i][NACT > 1 ? 1 : 0] : a[i][0];
-            reg_pivot<NQ>(v, done, k + 1, lane, s_l + (par ^ 1) * Np, s_pv[par ^ 1], s_row);
-        }
-        if (NACT > 2) reg_update<NQ, NS, 2, NACT>(a, l, ph, pl);
-        {
-            const double ub = __shfl_sync(0xffffffffu, sel_row<NQ>(b, ph), pl);
-#pragma unroll
-            for (int i = 0; i < NQ; i++) b[i] -= l[i] * ub;
-        }
-        __syncthreads();
-    }
-    // the finished column block goes to shared memory (U of the back substitution), the slots shift down
-#pragma unroll
-    for (int i = 0; i < NQ; i++) {
-        M[(size_t)(lane + 32 * i) * ldm + w + 8 * KB] = a[i][0];
-#pragma unroll
-        for (int j = 0; j + 1 < NACT; j++) a[i][j] = a[i][j + 1];
-    }
-}
-
-template <int NQ, int NS, int KB> struct RegLuBlocks {
-    static __device__ __forceinline__ void run(double (&a)[NQ][NS], double (&b)[NQ], unsigned& done, double* M, int ldm, short* s_row,
-                                               double* s_l, int (*s_pv)[4], int w, int lane)
-    {
-        reg_lu_block<NQ, NS, KB>(a, b, done, M, ldm, s_row, s_l, s_pv, w, lane);
-        RegLuBlocks<NQ, NS, KB + 1>::run(a, b, done, M, ldm, s_row, s_l, s_pv, w, lane);
-    }
-};
-template <int NQ, int NS> struct RegLuBlocks<NQ, NS, NS> {
-    static __device__ __forceinline__ void run(double (&)[NQ][NS], double (&)[NQ], unsigned&, double*, int, short*, double*, int (*)[4], int, int) {}
-};
-
-// M (shared, [Np][ldm], rhs in column Np) -> U in place (physical rows), eliminated rhs in column Np, s_row[k] = pivot row
-// of step k.  All FUSED_THREADS threads call it; ends with a barrier.
-template <int NQ>
-__device__ __forceinline__ void fused_lu_regs(double* M, int ldm, short* s_row, double* s_l, int (*s_pv)[4], int w, int lane)
-{
-    constexpr int Np = 32 * NQ, NS = Np / 8;
-    double a[NQ][NS], b[NQ];
-    unsigned done = 0u;
-#pragma unroll
-    for (int i = 0; i < NQ; i++) {
-        const double* Mr = M + (size_t)(lane + 32 * i) * ldm;
-#pragma unroll
-        for (int j = 0; j < NS; j++) a[i][j] = Mr[w + 8 * j];
-        b[i] = Mr[Np];
-    }
-    if (w == 0) {
-        double v[NQ];
-#pragma unroll
-        for (int i = 0; i < NQ; i++) v[i] = a[i][0];
-        reg_pivot<NQ>(v, 0u, 0, lane, s_l, s_pv[0], s_row);
-    }
-    __syncthreads();
-    RegLuBlocks<NQ, NS, 0>::run(a, b, done, M, ldm, s_row, s_l, s_pv, w, lane);
-    if (w == 0) {
-#pragma unroll
-        for (int i = 0; i < NQ; i++) M[(size_t)(lane + 32 * i) * ldm + Np] = b[i];
-    }
-    __syncthreads();
-}
-
-// ------------------------------------------------------------------------------------------------------------------
-// The same register-resident LU for a dimension n that is NOT a multiple of 32 (96 < n <= 32 NQ, the unpadded matrices of
-// fused_dim: o-H2O at the reference driver's N = 150).  Differences: the right-hand side is column n of the matrix and rides
-// in the slot of the warp that owns that column (no per-warp copy: the registers are needed for the 5 x 19 matrix entries
-// per thread), rows >= n are marked as used from the start and never loaded or stored, a block runs min(8, n - 8 KB) steps,
-// and NS = n / 8 + 1 slots cover the columns 0 .. n.
-// ------------------------------------------------------------------------------------------------------------------
-template <int NQ, int NS, int KB>
-__device__ __forceinline__ void regn_lu_block(double (&a)[NQ][NS], unsigned& done, double* M, int ldm, int n, short* s_row, double* s_l,
+__device__ __forceinline__ void reg_lu_block(double (&a)[NQ][NS], unsigned& done, double* M, int ldm, int n, short* s_row, double* s_l,
                                               int (*s_pv)[4], int w, int lane)
 {
     constexpr int Np = 32 * NQ, NACT = NS - KB;
@@ -378,20 +256,20 @@ __device__ __forceinline__ void regn_lu_block(double (&a)[NQ][NS], unsigned& don
         for (int j = 0; j + 1 < NACT; j++) a[i][j] = a[i][j + 1];
     }
 }
-template <int NQ, int NS, int KB> struct RegnLuBlocks {
+template <int NQ, int NS, int KB> struct RegLuBlocks {
     static __device__ __forceinline__ void run(double (&a)[NQ][NS], unsigned& done, double* M, int ldm, int n, short* s_row, double* s_l,
                                                int (*s_pv)[4], int w, int lane)
     {
-        regn_lu_block<NQ, NS, KB>(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
-        RegnLuBlocks<NQ, NS, KB + 1>::run(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
+        reg_lu_block<NQ, NS, KB>(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
+        RegLuBlocks<NQ, NS, KB + 1>::run(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
     }
 };
-template <int NQ, int NS> struct RegnLuBlocks<NQ, NS, NS> {
+template <int NQ, int NS> struct RegLuBlocks<NQ, NS, NS> {
     static __device__ __forceinline__ void run(double (&)[NQ][NS], unsigned&, double*, int, int, short*, double*, int (*)[4], int, int) {}
 };
 // n <= 8 NS - 1 and n <= 32 NQ (checked by the launcher).  All FUSED_THREADS threads call it; ends with a barrier.
 template <int NQ, int NS>
-__device__ __forceinline__ void fused_lu_regs_n(double* M, int ldm, int n, short* s_row, double* s_l, int (*s_pv)[4], int w, int lane)
+__device__ __forceinline__ void fused_lu_regs(double* M, int ldm, int n, short* s_row, double* s_l, int (*s_pv)[4], int w, int lane)
 {
     double a[NQ][NS];
     unsigned done = 0u;
@@ -410,13 +288,17 @@ __device__ __forceinline__ void fused_lu_regs_n(double* M, int ldm, int n, short
         reg_pivot<NQ>(v, done, 0, lane, s_l, s_pv[0], s_row);
     }
     __syncthreads();
-    RegnLuBlocks<NQ, NS, 0>::run(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
+    RegLuBlocks<NQ, NS, 0>::run(a, done, M, ldm, n, s_row, s_l, s_pv, w, lane);
     __syncthreads();
 }
 
-// LUV: 1..3 = register-resident LU with NQ = LUV (Np = 32 LUV), 4..5 = the same for an unpadded dimension (NQ = LUV,
-// 96 < n <= 128 and 128 < n <= 151), 0 = LU in shared memory (any Np <= 160).  One kernel per
-// variant so that the register allocation of the small, common sizes (two CTAs per SM) is not set by the large ones.
+// column slots of the register LU with NQ row slots: n / 8 + 1 for the largest n of the class (32, 62, 96, 128, 150)
+__host__ __device__ constexpr int fused_lu_slots(int nq) { return nq == 1 ? 5 : nq == 2 ? 8 : nq == 3 ? 13 : nq == 4 ? 17 : 19; }
+__host__ __device__ inline int fused_lu_variant(int n) { return n <= 32 ? 1 : n <= 62 ? 2 : n <= 96 ? 3 : n <= 128 ? 4 : n <= 150 ? 5 : 0; }
+
+// LUV: 1..5 = register-resident LU with NQ = LUV row slots (n <= 32, 62, 96, 128, 150), 0 = LU in shared memory (n <= 160).
+// One kernel per variant so that the register allocation of the small, common sizes (two CTAs per SM) is not set by the
+// large ones.
 // CS: molecule constants staged in shared memory (false: the matrix needs the room; they are read through L1/L2).
 template <int LUV, bool CS = true>
 __global__ void __launch_bounds__(FUSED_THREADS, (LUV == 1 || LUV == 2) ? 2 : 1)
@@ -445,7 +327,7 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     if (fused_c_in_smem(Np)) {
         double* s_C = arena;
         ldc = Np + 1; // odd stride: the assembly reads 8 rows per warp
-        for (int e = tid; e < Np * Np; e += FUSED_THREADS) s_C[(e / Np) * ldc + e % Np] = C[e];
+        for (int e = tid; e < Np * Np; e += FUSED_THREADS) s_C[(e / Np) * ldc + e % Np] = C[(size_t)(e / Np) * NpG + e % Np];
         C = s_C;
         arena += (size_t)Np * ldc;
     }
@@ -620,8 +502,7 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         //    (packed 64-bit keys, two REDUX max), interchanges the two positions and computes 1/pivot;
         //  * warps 1-7 apply step k to columns k+2 .. Np (rhs) as a 14 x 16 thread grid.
         // Values that agree in their top 56 bits count as ties (relative difference < 3e-14: immaterial for the pivot).
-        if constexpr (LUV >= 4) fused_lu_regs_n<LUV, LUV == 4 ? 17 : 19>(M, ldm, Np, s_row, s_l, s_pv, warp, lane); // o-H2O N = 150
-        else if constexpr (LUV > 0) fused_lu_regs<LUV>(M, ldm, s_row, s_l, s_pv, warp, lane); // Np = 64: OH, NH3, H2CO
+        if constexpr (LUV > 0) fused_lu_regs<LUV, fused_lu_slots(LUV)>(M, ldm, Np, s_row, s_l, s_pv, warp, lane);
         else {
             for (int r = tid; r < Np; r += FUSED_THREADS) s_row[r] = (short)r;
             __syncthreads();
@@ -669,8 +550,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         }
         if (warp == 0) {
             if constexpr (LUV > 0 && LUV <= 3) fused_backsolve<LUV>(M, ldm, Np, s_row, gnew, lane);
-            else if (Np <= 128) fused_backsolve_n<4>(M, ldm, Np, s_row, gnew, lane);
-            else fused_backsolve_n<5>(M, ldm, Np, s_row, gnew, lane);
+            else if (Np <= 128) fused_backsolve<4>(M, ldm, Np, s_row, gnew, lane);
+            else fused_backsolve<5>(M, ldm, Np, s_row, gnew, lane);
         }
         __syncthreads();
         // ---- K3: controller step (iteration_control.h:84-137), shared with the multi-kernel path --------------------
@@ -689,19 +570,24 @@ void launch_fused_solve(const DevModel& d, cudaStream_t s, int nlay, int accel, 
     g_rt_launches++;
     const bool cs = fused_fits(d, true);
     const size_t smem = fused_smem_doubles(d, cs) * sizeof(double);
-    switch (d.Np) {
-    case 32: k_fused_solve<1><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
-    case 64: k_fused_solve<2><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
-    case 96: k_fused_solve<3><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
-    default: {
-        const int n = fused_dim(d), v = g_fused_shared_lu ? 0 : n <= 128 ? 4 : n <= 151 ? 5 : 0;
-        if (v == 4 && cs) k_fused_solve<4, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
-        else if (v == 4) k_fused_solve<4, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
-        else if (v == 5 && cs) k_fused_solve<5, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
-        else if (v == 5) k_fused_solve<5, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
-        else if (cs) k_fused_solve<0, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+    const int n = fused_dim(d);
+    int v = fused_lu_variant(n);
+    if (v >= 4 && g_fused_shared_lu) v = 0;
+    switch (v) {
+    case 1: k_fused_solve<1><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
+    case 2: k_fused_solve<2><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
+    case 3: k_fused_solve<3><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err); break;
+    case 4:
+        if (cs) k_fused_solve<4, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        else k_fused_solve<4, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        break;
+    case 5:
+        if (cs) k_fused_solve<5, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        else k_fused_solve<5, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
+        break;
+    default:
+        if (cs) k_fused_solve<0, true><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
         else k_fused_solve<0, false><<<nlay, FUSED_THREADS, smem, s>>>(d, nlay, accel, max_iter, min_err);
-    }
     }
 }
 
