@@ -71,19 +71,20 @@ __device__ __forceinline__ unsigned long long pivot_key(double v, int off)
 }
 
 // back substitution by one warp, NQ position slots per lane (n <= 32 NQ: lanes beyond n idle along), right-looking, no
-// barriers
+// barriers.  Rows are scaled by 1 / U_rr as they are read (off the dependency chain), so that a step of the chain is one
+// shuffle (the finished x_i) and one fused multiply-add:  c_r = b_r / U_rr,  c_r -= (U_ri / U_rr) x_i,  x_r = c_r.
 template <int NQ>
 __device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int n, const short* rowf, double* gnew, int lane)
 {
-    double b[NQ], rd[NQ];
+    double c[NQ], rd[NQ];
     const double* rowp[NQ];
 #pragma unroll
     for (int q = 0; q < NQ; q++) {
         const int r = lane + 32 * q;
         const bool ok = r < n;
         rowp[q] = M + (size_t)rowf[ok ? r : 0] * ldm;
-        b[q] = ok ? rowp[q][n] : 0.;
         rd[q] = ok ? __drcp_rn(rowp[q][r]) : 0.;
+        c[q] = ok ? rowp[q][n] * rd[q] : 0.;
     }
 #pragma unroll
     for (int qi = NQ - 1; qi >= 0; qi--) {
@@ -91,16 +92,15 @@ __device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int n,
         for (int ii = 31; ii >= 0; ii--) {
             const int i = 32 * qi + ii;
             if (i >= n) continue; // uniform
-            const double xi = __shfl_sync(0xffffffffu, b[qi] * rd[qi], ii);
+            const double xi = __shfl_sync(0xffffffffu, c[qi], ii);
 #pragma unroll
-            for (int q = 0; q < qi; q++) b[q] -= rowp[q][i] * xi;
-            if (lane < ii) b[qi] -= rowp[qi][i] * xi;
-            else if (lane == ii) b[qi] = xi;
+            for (int q = 0; q < qi; q++) c[q] -= __dmul_rn(rowp[q][i], rd[q]) * xi;
+            if (lane < ii) c[qi] -= __dmul_rn(rowp[qi][i], rd[qi]) * xi;
         }
     }
 #pragma unroll
     for (int q = 0; q < NQ; q++)
-        if (lane + 32 * q < n) gnew[lane + 32 * q] = b[q];
+        if (lane + 32 * q < n) gnew[lane + 32 * q] = c[q];
 }
 
 // ------------------------------------------------------------------------------------------------------------------
