@@ -73,6 +73,8 @@ __device__ __forceinline__ unsigned long long pivot_key(double v, int off)
 // back substitution by one warp, NQ position slots per lane (n <= 32 NQ: lanes beyond n idle along), right-looking, no
 // barriers.  Rows are scaled by 1 / U_rr as they are read (off the dependency chain), so that a step of the chain is one
 // shuffle (the finished x_i) and one fused multiply-add:  c_r = b_r / U_rr,  c_r -= (U_ri / U_rr) x_i,  x_r = c_r.
+// (ncu, OH: with the loads left inside the unrolled chain every step waited for its own shared-memory load: ~120 cycles per
+// step, 12 % of the iteration with the other seven warps at the barrier.)
 template <int NQ>
 __device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int n, const short* rowf, double* gnew, int lane)
 {
@@ -86,16 +88,29 @@ __device__ __forceinline__ void fused_backsolve(const double* M, int ldm, int n,
         rd[q] = ok ? __drcp_rn(rowp[q][r]) : 0.;
         c[q] = ok ? rowp[q][n] * rd[q] : 0.;
     }
+    // eight steps at a time: first the scaled entries of the eight columns (independent loads), then the chain itself
 #pragma unroll
     for (int qi = NQ - 1; qi >= 0; qi--) {
-#pragma unroll 8
-        for (int ii = 31; ii >= 0; ii--) {
-            const int i = 32 * qi + ii;
-            if (i >= n) continue; // uniform
-            const double xi = __shfl_sync(0xffffffffu, c[qi], ii);
+#pragma unroll 1
+        for (int i0 = 32 * qi + 31; i0 >= 32 * qi; i0 -= 8) {
+            if (i0 - 7 >= n) continue; // uniform
+            double sc[NQ][8];
+            // columns >= n and, in the diagonal slot, the rows at or below the diagonal get a zero: the chain below is
+            // branch-free (two shuffles and one multiply-add per step)
 #pragma unroll
-            for (int q = 0; q < qi; q++) c[q] -= __dmul_rn(rowp[q][i], rd[q]) * xi;
-            if (lane < ii) c[qi] -= __dmul_rn(rowp[qi][i], rd[qi]) * xi;
+            for (int t = 0; t < 8; t++) {
+                const bool in = i0 - t < n;
+                const int i = in ? i0 - t : 0;
+#pragma unroll
+                for (int q = 0; q < qi; q++) sc[q][t] = in ? __dmul_rn(rowp[q][i], rd[q]) : 0.;
+                sc[qi][t] = in && lane < ((i0 - t) & 31) ? __dmul_rn(rowp[qi][i], rd[qi]) : 0.;
+            }
+#pragma unroll
+            for (int t = 0; t < 8; t++) {
+                const double xi = __shfl_sync(0xffffffffu, c[qi], (i0 - t) & 31);
+#pragma unroll
+                for (int q = 0; q <= qi; q++) c[q] -= sc[q][t] * xi;
+            }
         }
     }
 #pragma unroll
