@@ -463,7 +463,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
         }
         __syncthreads();
         // ---- K1b: M = C + R, row 0 = 1, rhs = e0, df = e0 - M pop (iteration_lvg.cpp:112-161); one warp per row ------
-        // four lanes per row: 64 rows in flight, two shuffle steps per reduction
+        // four lanes per row: 64 rows in flight, two shuffle steps per reduction (a whole warp per row -- coalesced loads of
+        // C where it is read from L2, N > 96 -- was measured at N = 150: 168 vs 151 us per iteration, slower)
         double eqmax = 0.;
         {
             const int q = tid & 3;

@@ -9,7 +9,12 @@ from radiative_transfer_b200 import solver, synthetic
 cfg = sys.argv[1] if len(sys.argv) > 1 else "ch3oh"
 L = int(sys.argv[2]) if len(sys.argv) > 2 else 200
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
-p = {"ch3oh": synthetic.config_ch3oh, "h2o": synthetic.config_h2o}[cfg](L=L) if cfg in ("ch3oh", "h2o") else synthetic.config_oh(L=L, overlap=(cfg == "oh_overlap"))
+if cfg in ("ch3oh", "h2o"):
+    p = {"ch3oh": synthetic.config_ch3oh, "h2o": synthetic.config_h2o}[cfg](L=L)
+elif cfg == "h2o150":
+    p = synthetic.config_h2o(L=L, N=150)
+else:
+    p = synthetic.config_oh(L=L, overlap=(cfg == "oh_overlap"))
 m = solver.Model(p)
 
 def timed(max_iter):
