@@ -117,7 +117,8 @@ def test_golden_lim_luminosity(gpu_results, case):
 # ---- live against the oracle, other sizes / seeds ---------------------------------------------------------------
 @pytest.mark.parametrize("name,L", [("generic", 9), ("oh", 5), ("oh_overlap", 5), ("ch3oh_small", 8), ("ch3oh_mid", 4),
                                     ("h2o_small", 3), ("h2o_odd", 5), ("nh3", 6), ("h2co", 6),
-                                    ("edge33", 1), ("edge98", 3), ("edge128", 2), ("edge136", 2), ("edge152", 2), ("edge161", 2)])
+                                    ("edge4", 3), ("edge9", 3), ("edge32", 3), ("edge33", 1), ("edge62", 3), ("edge64", 3), ("edge98", 3),
+                                    ("edge128", 2), ("edge136", 2), ("edge152", 2), ("edge161", 2)])
 def test_live_solve_vs_oracle(solver_mod, best_checker, problems, name, L):
     p = problems(name, L)
     m = solver_mod.Model(p)
