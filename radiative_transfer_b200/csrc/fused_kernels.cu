@@ -152,19 +152,22 @@ __device__ __forceinline__ void reg_pivot(const double (&v)[NQ], unsigned done, 
     unsigned hmax = 0u;
     int bi = 0;
     bool dup = false;
+    double vbest = 0.; // the lane's candidate travels with its key: the winner's value and slot are two independent shuffles
 #pragma unroll
     for (int i = 0; i < NQ; i++) {
         const unsigned h = (done >> i) & 1u ? 0u : ((unsigned)__double2hiint(v[i]) & 0x7fffffffu);
         dup = (h == hmax && h != 0u) || (dup && h < hmax);
-        if (h > hmax) { hmax = h; bi = i; }
+        if (h > hmax) { hmax = h; bi = i; vbest = v[i]; }
     }
     const unsigned mhi = __reduce_max_sync(0xffffffffu, hmax);
     const unsigned vote = __ballot_sync(0xffffffffu, hmax == mhi);
     const unsigned vdup = __ballot_sync(0xffffffffu, dup && hmax == mhi);
     int wl, wi;
+    double piv;
     if (mhi != 0u && __popc(vote) == 1 && vdup == 0u) {
         wl = __ffs(vote) - 1;
         wi = __shfl_sync(0xffffffffu, bi, wl);
+        piv = __shfl_sync(0xffffffffu, vbest, wl);
     }
     else {
         unsigned long long mykey[NQ], key = 0ull;
@@ -184,9 +187,9 @@ __device__ __forceinline__ void reg_pivot(const double (&v)[NQ], unsigned done, 
             if (mykey[i] == win) myi = i;
         wl = __ffs(__ballot_sync(0xffffffffu, myi >= 0)) - 1;
         wi = __shfl_sync(0xffffffffu, myi, wl);
+        piv = __shfl_sync(0xffffffffu, sel_row<NQ>(v, wi), wl);
     }
     const int p1 = wl + 32 * wi;
-    const double piv = __shfl_sync(0xffffffffu, sel_row<NQ>(v, wi), wl);
     const double rp = piv != 0. ? __drcp_rn(piv) : 0.; // 0: zero pivot, the column is left as is
 #pragma unroll
     for (int i = 0; i < NQ; i++) {
