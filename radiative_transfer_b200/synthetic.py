@@ -404,17 +404,17 @@ def small(name: str, L: int = 6) -> Problem:
     if name == "h2o_small":
         return config_h2o(L=L, N=150, cloud_kw=H2O_THICK_CLOUD)
     if name in ("edge4", "edge9", "edge32", "edge33", "edge62", "edge64", "edge98", "edge128", "edge136", "edge152", "edge161"):
-        # level counts at the seams of the solver's size classes: 33 (one level into the second 32-block of the register LU),
-        # 98 (just above the padded register-resident sizes: unpadded register LU, four row slots), 128 and 136 (multiples of 8:
-        # the right-hand side is alone in the last column block; 128 fills the four row slots, 136 is in the five-slot class),
-        # 152 (above the unpadded register LU: LU in shared memory), 161 (just above the fused kernel: blocked LU)
-        # 4 and 9 (fewer levels than one column block; odd), 32, 62 and 64 (the ends of the one- and two-row-slot classes)
+        # level counts at the seams of the solver's size classes (row slots per lane of the fused solver's register LU):
+        # 4 and 9 (fewer levels than one column block; odd), 32, 33, 62 and 64 (the ends of the one- and two-slot classes),
+        # 98 (first of the four-slot class), 128 and 136 (multiples of 8: the right-hand side is alone in the last column
+        # block; 128 fills the four row slots, 136 is in the five-slot class), 152 (above the register LU: LU in shared
+        # memory), 161 (just above the fused kernel: blocked multi-kernel LU)
         shape = {"edge4": (1, 1, 4), "edge9": (1, 3, 3), "edge32": (1, 4, 8), "edge33": (1, 3, 11), "edge62": (1, 2, 31),
                  "edge64": (1, 8, 8), "edge98": (2, 7, 7), "edge128": (2, 8, 8), "edge136": (1, 8, 17), "edge152": (1, 8, 19),
                  "edge161": (1, 7, 23)}[name]
         return config_ch3oh(L=L, n_vt=shape[0], n_k=shape[1], n_j=shape[2])
     if name == "h2o_odd":
-        return config_h2o(L=L, N=131)  # odd level count between the register-resident and the blocked LU sizes
+        return config_h2o(L=L, N=131)  # odd level count in the five-row-slot class of the fused solver's register LU
     if name == "nh3":
         return config_nh3(L=L)
     if name == "h2co":
