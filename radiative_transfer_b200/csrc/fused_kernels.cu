@@ -45,6 +45,10 @@ __host__ __device__ inline size_t fused_smem_doubles(const DevModel& d, bool cs)
     return Nm * (Nm + 1) + Nm + 2 * R + 64 + (fused_c_in_smem(d.Np) ? Nm * (Nm + 1) : 0) + (cs ? fused_const_doubles(d) : 0);
 }
 static bool fused_fits(const DevModel& d, bool cs);
+__device__ __forceinline__ void fused_cp_async8(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
 
 // Arg-max of the 64-bit keys of warp 0 (two REDUX), interchange of positions k <-> p in s_row, publication of the pivot's
 // physical row, the displaced row, p and 1/pivot for parity k & 1.  key = |a| bits with the low byte replaced by
@@ -422,6 +426,14 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     for (;;) {
         // ---- populations of this step (the controller left them in global memory) ----------------------------------
         for (int j = tid; j < Np; j += FUSED_THREADS) s_pop[j] = j < N ? gpop[j] : 0.;
+        // N > 96 (C is read from global memory / L2): the copy M = C starts here as 8-byte asynchronous copies -- M is free
+        // since the back substitution -- and lands while the intensities are computed; the assembly then patches in place
+        constexpr bool C_ASYNC = !(LUV >= 1 && LUV <= 3);
+        if (C_ASYNC && !fused_c_in_smem(Np)) {
+            for (int r = warp; r < Np; r += FUSED_THREADS / 32)
+                for (int c = lane; c < Np; c += 32) fused_cp_async8(M + (size_t)r * ldm + c, C + (size_t)r * ldc + c);
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        }
         __syncthreads();
         // ---- K1a: mean intensities -> radiative rates (iteration_lvg.cpp:163-185, :428-501) ------------------------
         const int ntask = s_ntask;
@@ -464,6 +476,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
                 s_yd[lb] = A2ul * (1. + J2); s_yu[lb] = A2lu * J2;
             }
         }
+        const bool m_is_c = C_ASYNC && !fused_c_in_smem(Np); // M holds C already (asynchronous copy above)
+        if (m_is_c) asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
         // ---- K1b: M = C + R, row 0 = 1, rhs = e0, df = e0 - M pop (iteration_lvg.cpp:112-161); one warp per row ------
         // four lanes per row: 64 rows in flight, two shuffle steps per reduction (a whole warp per row -- coalesced loads of
@@ -480,7 +494,12 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
                     for (int j = q; j < Np; j += 4) { const double v = j < N ? 1. : 0.; Mrow[j] = v; dot += v * s_pop[j]; }
                 }
                 else {
-                    for (int j = q; j < Np; j += 4) { const double c = Crow[j]; Mrow[j] = c; dot += c * s_pop[j]; }
+                    if (m_is_c) {
+                        for (int j = q; j < Np; j += 4) dot += Mrow[j] * s_pop[j];
+                    }
+                    else {
+                        for (int j = q; j < Np; j += 4) { const double c = Crow[j]; Mrow[j] = c; dot += c * s_pop[j]; }
+                    }
                     if (row < N) {
                         __syncwarp(gmask); // the row's copy is complete before its radiative entries are patched
                         double diag = 0.;
@@ -488,13 +507,13 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
                             const int col = c_rcol[e], ln = c_rline[e], line = ln >> 1;
                             const double off = (ln & 1) ? s_yd[line] : s_yu[line];
                             const double dg = (ln & 1) ? s_yu[line] : s_yd[line];
-                            Mrow[col] = Crow[col] + off;
+                            Mrow[col] = (m_is_c ? Mrow[col] : Crow[col]) + off;
                             dot += off * s_pop[col];
                             diag += dg;
                         }
                         diag += __shfl_xor_sync(gmask, diag, 1);
                         diag += __shfl_xor_sync(gmask, diag, 2);
-                        if (q == 0) { Mrow[row] = Crow[row] - diag; dot -= diag * s_pop[row]; }
+                        if (q == 0) { Mrow[row] = (m_is_c ? Mrow[row] : Crow[row]) - diag; dot -= diag * s_pop[row]; }
                     }
                 }
                 dot += __shfl_xor_sync(gmask, dot, 1);
