@@ -341,7 +341,8 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     __shared__ double s_l[2 * (LUV > 0 ? 32 * LUV : 1)]; // register-resident LU: multipliers of the column, double-buffered
     __shared__ int s_pv[2][4];                           //   pivot row of the column
     __shared__ double s_eq[FUSED_THREADS / 32];
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0); // warp-uniform by construction (the compiler keeps it in a uniform register)
     // the collisional matrix of the layer is constant over the iteration: staged in shared memory when it fits
     const double* C = d.Cmat + (size_t)lay * NpG * NpG;
     int ldc = NpG;
