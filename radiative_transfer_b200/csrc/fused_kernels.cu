@@ -342,7 +342,12 @@ k_fused_solve(DevModel d, int nlay, int accel, int max_iter, double min_err)
     __shared__ int s_pv[2][4];                           //   pivot row of the column
     __shared__ double s_eq[FUSED_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31;
-    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0); // warp-uniform by construction (the compiler keeps it in a uniform register)
+    // The warp index through a broadcast shuffle: the compiler then knows it is warp-uniform, keeps it in a uniform register
+    // and drops the divergence guards (BRA.DIV + reconvergence) it otherwise puts in front of every warp collective of the
+    // pivot search, which sits under `if (warp == owner)`: 38 -> 3 guards in the N = 56 kernel, OH 65.6 -> 59.7 ms per solve.
+    // (The same line in the kernels of the blocked LU made them slower -- 4.45 vs 4.33 ms per CH3OH iteration -- and is not
+    // used there.)
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     // the collisional matrix of the layer is constant over the iteration: staged in shared memory when it fits
     const double* C = d.Cmat + (size_t)lay * NpG * NpG;
     int ldc = NpG;
